@@ -1,0 +1,364 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle.
+
+One GPU is enough: N ranks are emulated in one cooperative launch that runs the same
+device code as the multi-GPU entry points (vllm_distributed_b200/emu.py).
+Bar: bit-exact for the all-reduce, the residual stream, the all-gather and send/recv;
+vLLM's own bf16 tolerance (atol 1e-3, rtol 1.6e-2) for the normalised output, whose row
+sum of squares is reduced in a different order than torch's CPU kernel.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import oracle  # noqa: E402  (checker only)
+
+ATOL = {torch.bfloat16: 1e-3, torch.float16: 1e-2, torch.float32: 1e-5}
+RTOL = {torch.bfloat16: 1.6e-2, torch.float16: 2e-3, torch.float32: 1.3e-6}
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    if not torch.cuda.is_available():
+        pytest.fail("-m gpu tests need a CUDA device")
+    import vllm_distributed_b200.comm as comm
+    import vllm_distributed_b200.emu as emu
+    from vllm_distributed_b200 import _cabi as C
+    return comm, emu, C
+
+
+_groups = {}
+
+
+def group(pkg, world, **kw):
+    comm, emu, C = pkg
+    key = (world, tuple(sorted(kw.items())))
+    if key not in _groups:
+        g = emu.EmuGroup(world, "cuda:0", **kw)
+        g.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, 3000)
+        _groups[key] = g
+    return _groups[key]
+
+
+def rand(shape, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(*shape, generator=g).to(dtype)
+
+
+def bits_equal(a, b):
+    a, b = a.cpu().contiguous(), b.cpu().contiguous()
+    return torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+
+
+def check_norm(y_gpu, y_ref, dtype):
+    torch.testing.assert_close(y_gpu.cpu().float(), y_ref.float(), atol=ATOL[dtype], rtol=RTOL[dtype])
+    if dtype != torch.float32:
+        mism = (y_gpu.cpu().view(torch.int16) != y_ref.view(torch.int16)).sum().item()
+        assert mism <= max(2, y_ref.numel() // 200), f"{mism} of {y_ref.numel()} differ"
+
+
+# ---- TP=1: the local norm kernels ------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("shape", [(1, 896), (5, 896), (64, 4096), (7, 8192), (3, 16384), (2, 8)])
+def test_world1_fused_add_rms_norm(pkg, dtype, shape):
+    comm, _, _ = pkg
+    if dtype == torch.float32 and shape[1] > 8192:
+        pytest.skip("fp32 rows above 8192 exceed the fused row kernel")
+    x, res, gamma = rand(shape, dtype, 1), rand(shape, dtype, 2), rand(shape[1:], dtype, 3)
+    y_ref, r_ref = oracle.fused_add_rms_norm(x, res, gamma, 1e-5)
+    xd, rd = x.cuda(), res.cuda()
+    comm.fused_add_rms_norm_(xd, rd, gamma.cuda(), 1e-5)
+    assert bits_equal(rd, r_ref)
+    check_norm(xd, y_ref, dtype)
+    y0_ref, _ = oracle.fused_add_rms_norm(x, None, gamma, 1e-6)
+    y0 = comm.rms_norm(x.cuda(), gamma.cuda(), 1e-6)
+    check_norm(y0, y0_ref, dtype)
+
+
+def test_world1_ctx_entry_point(pkg):
+    comm, _, C = pkg
+    c = comm.B200Comm(0, 1, None, 0, 0, 0, torch.device("cuda:0"))
+    x, res, gamma = rand((9, 4096), torch.bfloat16, 4), rand((9, 4096), torch.bfloat16, 5), rand((4096,), torch.bfloat16, 6)
+    y_ref, r_ref = oracle.fused_add_rms_norm(x, res, gamma, 1e-5)
+    y, r = c.all_reduce_add_rmsnorm(x.cuda(), res.cuda(), gamma.cuda(), 1e-5)
+    assert bits_equal(r, r_ref)
+    check_norm(y, y_ref, torch.bfloat16)
+    assert bits_equal(c.all_reduce(x.cuda()), x)
+    c.close()
+
+
+# ---- all-reduce ------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("variant", [1, 2])
+def test_all_reduce_bit_exact(pkg, world, variant):
+    g = group(pkg, world)
+    # a ragged sequence of sizes, back to back, exercises region rotation and re-arming
+    for i, (numel, dtype) in enumerate([(8, torch.bfloat16), (7 * 1000, torch.bfloat16),
+                                        (64 * 4096, torch.bfloat16), (4, torch.float32),
+                                        (3 * 896, torch.float16), (1 << 20, torch.bfloat16),
+                                        (5 * 8192, torch.float32), (24, torch.bfloat16)]):
+        xs = [rand((numel,), dtype, 100 * i + r) for r in range(world)]
+        ref = oracle.all_reduce(xs)
+        outs = g.all_reduce([x.cuda() for x in xs], variant=variant)
+        for r in range(world):
+            assert bits_equal(outs[r], ref), f"call {i} rank {r} numel {numel} {dtype}"
+    g.check_health()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_all_reduce_mixed_variants_and_auto(pkg, world):
+    g = group(pkg, world)
+    for i, (numel, variant) in enumerate([(4096, 1), (4096, 2), (512 * 1024, 0), (4096, 0),
+                                          (64, 2), (64, 1), (300000 * 8, 0)]):
+        xs = [rand((numel,), torch.bfloat16, 7 * i + r) for r in range(world)]
+        ref = oracle.all_reduce(xs)
+        for o in g.all_reduce([x.cuda() for x in xs], variant=variant):
+            assert bits_equal(o, ref)
+    g.check_health()
+
+
+def test_all_reduce_negative_zero_is_numerically_preserved(pkg):
+    g = group(pkg, 2)
+    x0 = torch.zeros(64, dtype=torch.bfloat16)
+    x0[1::2] = -0.0  # aligned (+0,-0) pairs are exactly the in-flight marker pattern
+    x1 = torch.zeros(64, dtype=torch.bfloat16)
+    x1[1::2] = -0.0
+    for variant in (1, 2):
+        outs = g.all_reduce([x0.cuda(), x1.cuda()], variant=variant)
+        assert torch.equal(outs[0].cpu().float(), torch.zeros(64))  # -0 == +0
+    f = torch.full((8,), -0.0, dtype=torch.float32)
+    outs = g.all_reduce([f.cuda(), f.clone().cuda()], variant=1)
+    assert torch.equal(outs[1].cpu(), torch.zeros(8))
+    g.check_health()
+
+
+# ---- fused all-reduce + residual + RMSNorm -------------------------------------------------
+
+FUSED_SHAPES = [(1, 896), (5, 896), (3, 4096), (64, 4096), (2, 8192), (33, 8192), (7, 1000),
+                (2, 16384)]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("variant", [1, 2])
+def test_fused_vs_oracle(pkg, world, variant):
+    g = group(pkg, world)
+    dtype = torch.bfloat16
+    for i, (t, h) in enumerate(FUSED_SHAPES):
+        xs = [rand((t, h), dtype, 1234 + r) for r in range(world)]
+        res, gamma = rand((t, h), dtype, 7), rand((h,), dtype, 8)
+        eps = 1e-5 if i % 2 else 1e-6
+        y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, eps)
+        ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs],
+                                          [res.cuda() for _ in range(world)], gamma.cuda(), eps,
+                                          variant=variant)
+        for r in range(world):
+            assert bits_equal(rs[r], r_ref), f"residual, shape {(t, h)} rank {r}"
+            assert bits_equal(ys[r], ys[0]), "ranks must agree bit for bit"
+        check_norm(ys[0], y_ref, dtype)
+    g.check_health()
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+def test_fused_other_dtypes(pkg, dtype):
+    g = group(pkg, 4)
+    for variant in (1, 2):
+        t, h = 6, 2048
+        xs = [rand((t, h), dtype, 50 + r) for r in range(4)]
+        res, gamma = rand((t, h), dtype, 7), rand((h,), dtype, 8)
+        y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+        ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs], [res.cuda() for _ in range(4)],
+                                          gamma.cuda(), 1e-5, variant=variant)
+        assert bits_equal(rs[3], r_ref)
+        check_norm(ys[2], y_ref, dtype)
+
+
+def test_fused_in_place_aliasing(pkg):
+    g = group(pkg, 4)
+    t, h = 17, 4096
+    for variant in (1, 2):
+        xs = [rand((t, h), torch.bfloat16, 300 + r) for r in range(4)]
+        res, gamma = rand((t, h), torch.bfloat16, 7), rand((h,), torch.bfloat16, 8)
+        y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+        xd = [x.cuda() for x in xs]
+        rd = [res.cuda() for _ in range(4)]
+        ys, rs = g.all_reduce_add_rmsnorm(xd, rd, gamma.cuda(), 1e-5, variant=variant, inplace=True)
+        assert ys[0].data_ptr() == xd[0].data_ptr() and rs[0].data_ptr() == rd[0].data_ptr()
+        for r in range(4):
+            assert bits_equal(rd[r], r_ref)
+        check_norm(xd[1], y_ref, torch.bfloat16)
+
+
+def test_fused_without_residual(pkg):
+    g = group(pkg, 2)
+    xs = [rand((4, 896), torch.bfloat16, 11 + r) for r in range(2)]
+    gamma = rand((896,), torch.bfloat16, 8)
+    ar = oracle.all_reduce(xs)
+    y_ref, _ = oracle.fused_add_rms_norm(ar, None, gamma, 1e-6)
+    ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs], None, gamma.cuda(), 1e-6, variant=1)
+    assert rs[0] is None
+    check_norm(ys[0], y_ref, torch.bfloat16)
+
+
+@pytest.mark.parametrize("name", ["qwen05b_tp2_b1", "qwen05b_tp2_b5", "llama8b_tp2_b3",
+                                  "llama70b_tp4_b2", "llama70b_tp8_b3", "ragged_tp4_b7_h1000"])
+def test_fused_vs_vllm_golden(pkg, golden_dir, name):
+    """Against the outputs of the reference's own vLLM path (gloo all-reduce + native norm)."""
+    gold = dict(np.load(os.path.join(golden_dir, name + ".npz")))
+    world, tokens, hidden = (int(v) for v in gold["meta"])
+    g = group(pkg, world)
+    xs = [oracle.from_bits(gold[f"x{r}"]).cuda() for r in range(world)]
+    res = oracle.from_bits(gold["residual"])
+    gamma = oracle.from_bits(gold["gamma"]).cuda()
+    eps = float(gold["eps"][0])
+    for variant in (1, 2):
+        ar = g.all_reduce(xs, variant=variant)[0].cpu()
+        ref_ar = oracle.from_bits(gold["ar"])
+        # north_star tolerance: <= 1e-2 relative on hidden states (gloo rounds every partial add)
+        assert float((ar.float() - ref_ar.float()).norm() / ref_ar.float().norm()) <= 1e-2
+        ys, rs = g.all_reduce_add_rmsnorm(xs, [res.cuda() for _ in range(world)], gamma, eps,
+                                          variant=variant)
+        ref_y, ref_r = oracle.from_bits(gold["norm_out"]), oracle.from_bits(gold["residual_out"])
+        for got, ref in ((ys[0].cpu(), ref_y), (rs[0].cpu(), ref_r)):
+            assert float((got.float() - ref.float()).norm() / ref.float().norm()) <= 1e-2
+        if world == 2:  # two addends: the sum is rounded once on both sides -> exact
+            assert bits_equal(ar, ref_ar) and bits_equal(rs[0], ref_r)
+
+
+# ---- all-gather --------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_all_gather_bit_exact(pkg, world):
+    g = group(pkg, world)
+    for i, (rows, cols, dtype) in enumerate([(1, 8, torch.bfloat16), (3, 520, torch.bfloat16),
+                                             (5, 16032, torch.bfloat16), (64, 2004, torch.float32),
+                                             (2, 1000, torch.float16), (7, 8, torch.bfloat16)]):
+        # random BYTES: NaN payloads, -0.0, denormals must all survive
+        gen = torch.Generator().manual_seed(900 + i)
+        slabs = [torch.randint(0, 256, (rows, cols * dtype.itemsize), generator=gen,
+                               dtype=torch.uint8).view(dtype) for _ in range(world)]
+        ref = oracle.all_gather_lastdim(slabs)
+        outs = g.all_gather_lastdim([s.cuda() for s in slabs])
+        for r in range(world):
+            assert outs[r].shape == ref.shape
+            assert bits_equal(outs[r], ref), f"call {i} rank {r}"
+    g.check_health()
+
+
+@pytest.mark.parametrize("name", ["ag_tp2", "ag_tp4", "ag_tp8"])
+def test_all_gather_vs_vllm_golden(pkg, golden_dir, name):
+    gold = dict(np.load(os.path.join(golden_dir, name + ".npz")))
+    world, rows, cols = (int(v) for v in gold["meta"])
+    g = group(pkg, world)
+    outs = g.all_gather_lastdim([oracle.from_bits(gold[f"slab{r}"]).cuda() for r in range(world)])
+    for o in outs:
+        assert np.array_equal(oracle.to_bits(o), gold["full"])
+
+
+# ---- pipeline send / recv -------------------------------------------------------------------------
+
+def test_sendrecv_bit_exact_and_credits(pkg):
+    g = group(pkg, 4)
+    gen = torch.Generator().manual_seed(5)
+    # more messages than mailbox slots, both directions, several pairs
+    for i in range(7):
+        for (src, dst) in ((0, 1), (1, 0), (2, 3), (0, 3)):
+            n = 16 * (1 + (i * 37 + src * 11 + dst) % 500)
+            t = torch.randint(0, 256, (n,), generator=gen, dtype=torch.uint8)
+            out = g.sendrecv(src, dst, t.cuda())
+            assert bits_equal(out, t)
+    g.check_health()
+
+
+def test_sendrecv_larger_than_mailbox_and_pp_golden(pkg, golden_dir):
+    g = group(pkg, 2, max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=64 * 1024)
+    gen = torch.Generator().manual_seed(6)
+    t = torch.randint(0, 256, (5 * 64 * 1024 + 160,), generator=gen, dtype=torch.uint8)
+    assert bits_equal(g.sendrecv(0, 1, t.cuda()), t)
+    # the reference's PP hop with TP slicing (parallel_state.py:913-916, 1014-1038)
+    gold = dict(np.load(os.path.join(golden_dir, "pp2_tp2.npz")))
+    tp = int(gold["meta"][0])
+    for key in ("hidden_states", "residual"):
+        full = oracle.from_bits(gold[f"{key}_in"])
+        slices = [g.sendrecv(0, 1, full.reshape(tp, -1)[t_].contiguous().cuda()) for t_ in range(tp)]
+        g2 = group(pkg, tp)
+        joined = g2.all_gather_lastdim([s.reshape(1, -1) for s in slices])[0].reshape(full.shape)
+        assert np.array_equal(oracle.to_bits(joined), gold[f"{key}_out_tp0"])
+
+
+# ---- CUDA graph replay, errors, full-size properties ----------------------------------------------
+
+def test_cuda_graph_replay(pkg):
+    g = group(pkg, 4)
+    t, h = 8, 4096
+    xs = [rand((t, h), torch.bfloat16, 40 + r).cuda() for r in range(4)]
+    res = [rand((t, h), torch.bfloat16, 7).cuda() for _ in range(4)]
+    gamma = rand((h,), torch.bfloat16, 8).cuda()
+    y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm([x.cpu() for x in xs], res[0].cpu(), gamma.cpu(), 1e-5)
+    ys = [torch.empty_like(x) for x in xs]
+    g.all_reduce_add_rmsnorm(xs, res, gamma, 1e-5, variant=1)  # warm up outside capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(graph, stream=s):
+            for variant in (1, 2, 1):  # three calls per replay: regions rotate inside the graph
+                ys, rs = g.all_reduce_add_rmsnorm(xs, res, gamma, 1e-5, variant=variant)
+    for _ in range(5):
+        for y in ys:
+            y.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert bits_equal(rs[2], r_ref)
+        check_norm(ys[3], y_ref, torch.bfloat16)
+    g.check_health()
+
+
+def test_error_codes(pkg):
+    comm, emu, C = pkg
+    g = group(pkg, 2, max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=64 * 1024)
+    big = torch.zeros((1 << 20) // 2 + 8, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(C.B200CError) as e:
+        g.all_reduce([big, big.clone()])
+    assert e.value.code == C.ETOOBIG
+    odd = torch.zeros(12, dtype=torch.bfloat16, device="cuda")  # 24 bytes: not a multiple of 16
+    with pytest.raises(C.B200CError) as e:
+        g.all_reduce([odd, odd.clone()])
+    assert e.value.code == C.EINVAL
+    x = torch.zeros(4, 12, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(C.B200CError):
+        comm.rms_norm(x, torch.ones(12, dtype=torch.bfloat16, device="cuda"), 1e-5)
+    # empty inputs are a no-op, as in the reference (numel == 0 tensors are skipped)
+    e0 = torch.zeros(0, 4096, dtype=torch.bfloat16, device="cuda")
+    outs = g.all_reduce([e0, e0.clone()])
+    assert outs[0].shape == (0, 4096)
+    g.check_health()
+
+
+def test_full_size_properties(pkg):
+    """BASELINE sweep maximum (8192 tokens x 8192 hidden, bf16 = 128 MiB): too slow for the CPU
+    oracle in a unit test, so check size-independent properties instead."""
+    g = group(pkg, 2, max_bytes=128 << 20, ag_bytes=1 << 20, p2p_bytes=1 << 20)
+    t, h = 8192, 8192
+    x = torch.randn(t, h, device="cuda", dtype=torch.bfloat16)
+    zero = torch.zeros_like(x)
+    for variant in (2, 1):
+        a = g.all_reduce([x, zero], variant=variant)           # identity: x + 0 == x
+        assert torch.equal(a[0], x) and torch.equal(a[1], x)
+        b = g.all_reduce([x, -x], variant=variant)             # inverse: x + (-x) == 0
+        assert not b[0].any()
+        c = g.all_reduce([x, x], variant=variant)              # doubling is exact in bf16
+        assert torch.equal(c[1], x * 2)
+    # fused: with zero residual and unit gamma every row of norm_out has mean square ~1
+    gamma = torch.ones(h, device="cuda", dtype=torch.bfloat16)
+    ys, rs = g.all_reduce_add_rmsnorm([x, zero], [zero, zero.clone()], gamma, 1e-5, variant=2)
+    assert torch.equal(rs[0], x) and torch.equal(ys[0], ys[1])
+    ms = ys[0].float().pow(2).mean(-1)
+    assert float((ms - 1).abs().max()) < 2e-2
+    g.check_health()
+    g.close()
+    _groups.pop((2, tuple(sorted(dict(max_bytes=128 << 20, ag_bytes=1 << 20, p2p_bytes=1 << 20).items()))), None)

@@ -1,0 +1,219 @@
+"""Torch-facing host objects over the C ABI: one `B200Comm` per (process, group).
+
+PyTorch is plumbing here (device memory, streams, the gloo group used once to swap IPC
+handles); the arithmetic and the exchange run in libb200c.so.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import byref, c_longlong, c_size_t, c_void_p
+
+import torch
+
+from . import _cabi as C
+
+DTYPE_CODE = {torch.bfloat16: C.BF16, torch.float16: C.F16, torch.float32: C.F32}
+
+# Arena defaults, sized for B200's 180 GB: 64 MiB messages cover [4096 tok x 8192] bf16
+# (three rotating regions of 2x that), 72 MiB covers the 70B lm_head gather at batch 256.
+DEFAULT_MAX_BYTES = int(os.environ.get("B200C_MAX_BYTES", 64 << 20))
+DEFAULT_AG_BYTES = int(os.environ.get("B200C_AG_BYTES", 72 << 20))
+DEFAULT_P2P_BYTES = int(os.environ.get("B200C_P2P_BYTES", 16 << 20))
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: torch.Tensor | None) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def arena_bytes(world: int, max_bytes: int, ag_bytes: int, p2p_bytes: int) -> int:
+    out = c_size_t(0)
+    C.check(C.lib().b200c_arena_bytes(world, max_bytes, ag_bytes, p2p_bytes, byref(out)))
+    return out.value
+
+
+def alloc_shared(nbytes: int) -> tuple[int, bytes]:
+    """cudaMalloc on the current device + its IPC handle."""
+    ptr = c_void_p(0)
+    handle = C.Handle()
+    C.check(C.lib().b200c_alloc_shared(nbytes, byref(ptr), handle))
+    return ptr.value, bytes(handle)
+
+
+def open_handle(handle: bytes) -> int:
+    ptr = c_void_p(0)
+    h = C.Handle.from_buffer_copy(handle)
+    C.check(C.lib().b200c_open_handle(h, byref(ptr)))
+    return ptr.value
+
+
+# ---- standalone norm ops (TP=1 and the unfused path; no communicator state) ----------------
+
+def _rows(x: torch.Tensor) -> tuple[int, int]:
+    hidden = x.shape[-1]
+    return x.numel() // hidden if hidden else 0, hidden
+
+
+def fused_add_rms_norm_(x: torch.Tensor, residual: torch.Tensor, gamma: torch.Tensor,
+                        eps: float) -> tuple[torch.Tensor, torch.Tensor]:
+    """In place: residual += x; x = rmsnorm(residual) * gamma.  (vLLM _C.fused_add_rms_norm)"""
+    assert x.is_cuda and x.is_contiguous() and residual.is_contiguous()
+    tokens, hidden = _rows(x)
+    C.check(C.lib().b200c_fused_add_rms_norm(x.data_ptr(), residual.data_ptr(), gamma.data_ptr(),
+                                             float(eps), tokens, hidden, DTYPE_CODE[x.dtype],
+                                             _stream()))
+    return x, residual
+
+
+def rms_norm(x: torch.Tensor, gamma: torch.Tensor, eps: float,
+             out: torch.Tensor | None = None) -> torch.Tensor:
+    assert x.is_cuda and x.is_contiguous()
+    out = torch.empty_like(x) if out is None else out
+    tokens, hidden = _rows(x)
+    C.check(C.lib().b200c_rms_norm(out.data_ptr(), x.data_ptr(), gamma.data_ptr(), float(eps),
+                                   tokens, hidden, DTYPE_CODE[x.dtype], _stream()))
+    return out
+
+
+class B200Comm:
+    """One rank of a TP (or PP) group.  Owns its arena and the peers' IPC mappings."""
+
+    def __init__(self, rank: int, world: int, arena_ptrs: list[int] | None, max_bytes: int,
+                 ag_bytes: int, p2p_bytes: int, device: torch.device, owned_arena: int = 0,
+                 opened: list[int] | None = None):
+        self.rank, self.world, self.device = rank, world, device
+        self.max_bytes, self.ag_bytes, self.p2p_bytes = max_bytes, ag_bytes, p2p_bytes
+        self._owned_arena = owned_arena
+        self._opened = opened or []
+        ctx = c_void_p(0)
+        arr = C.ptr_array(arena_ptrs) if arena_ptrs else None
+        with torch.cuda.device(device):
+            C.check(C.lib().b200c_init(rank, world, arr, max_bytes, ag_bytes, p2p_bytes, byref(ctx)))
+        self.ctx = ctx
+
+    # ---- construction over a torch.distributed CPU group (one process per GPU) ----
+    @classmethod
+    def from_process_group(cls, cpu_group, device: torch.device,
+                           max_bytes: int = DEFAULT_MAX_BYTES, ag_bytes: int = DEFAULT_AG_BYTES,
+                           p2p_bytes: int = DEFAULT_P2P_BYTES) -> "B200Comm":
+        import torch.distributed as dist
+        rank = dist.get_rank(cpu_group)
+        world = dist.get_world_size(cpu_group)
+        if world == 1:
+            return cls(0, 1, None, 0, 0, 0, device)
+        nbytes = arena_bytes(world, max_bytes, ag_bytes, p2p_bytes)
+        with torch.cuda.device(device):
+            mine, handle = alloc_shared(nbytes)
+            handles: list = [None] * world
+            dist.all_gather_object(handles, handle, group=cpu_group)
+            ptrs, opened = [], []
+            for r in range(world):
+                if r == rank:
+                    ptrs.append(mine)
+                else:
+                    p = open_handle(handles[r])
+                    ptrs.append(p)
+                    opened.append(p)
+            comm = cls(rank, world, ptrs, max_bytes, ag_bytes, p2p_bytes, device,
+                       owned_arena=mine, opened=opened)
+        # every arena must be armed before any rank pushes into it
+        dist.barrier(group=cpu_group)
+        return comm
+
+    # ---- tuning ----
+    def set_tuning(self, key: int, value: int) -> None:
+        C.check(C.lib().b200c_set_tuning(self.ctx, key, int(value)))
+
+    def get_tuning(self, key: int) -> int:
+        v = c_longlong(0)
+        C.check(C.lib().b200c_get_tuning(self.ctx, key, byref(v)))
+        return v.value
+
+    def check_health(self) -> None:
+        C.check(C.lib().b200c_query_error(self.ctx))
+
+    # ---- predicates the communicator uses to decide between this path and NCCL ----
+    def can_all_reduce(self, x: torch.Tensor) -> bool:
+        nbytes = x.numel() * x.element_size()
+        return (x.is_cuda and x.dtype in DTYPE_CODE and x.is_contiguous() and nbytes % 16 == 0
+                and 0 < nbytes <= self.max_bytes and x.data_ptr() % 16 == 0)
+
+    def can_fuse_norm(self, x: torch.Tensor) -> bool:
+        hidden = x.shape[-1]
+        return (self.can_all_reduce(x) and (hidden * x.element_size()) % 16 == 0
+                and hidden * x.element_size() // 16 <= 2048)
+
+    def can_all_gather_lastdim(self, x: torch.Tensor) -> bool:
+        row_bytes = x.shape[-1] * x.element_size()
+        return (x.is_cuda and x.is_contiguous() and row_bytes % 16 == 0 and x.numel() > 0
+                and x.numel() * x.element_size() * self.world <= self.ag_bytes
+                and x.data_ptr() % 16 == 0)
+
+    def can_p2p(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return t.is_cuda and t.is_contiguous() and nbytes % 16 == 0 and t.data_ptr() % 16 == 0
+
+    # ---- the hot path ----
+    def all_reduce(self, x: torch.Tensor, variant: int = C.AUTO,
+                   out: torch.Tensor | None = None) -> torch.Tensor:
+        out = torch.empty_like(x) if out is None else out
+        C.check(C.lib().b200c_all_reduce(self.ctx, x.data_ptr(), out.data_ptr(), x.numel(),
+                                         DTYPE_CODE[x.dtype], variant, _stream()))
+        return out
+
+    def all_reduce_add_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor | None,
+                               gamma: torch.Tensor, eps: float, variant: int = C.AUTO,
+                               inplace: bool = False) -> tuple[torch.Tensor, torch.Tensor | None]:
+        """-> (norm_out, residual_out).  inplace: norm_out aliases x, residual_out aliases residual."""
+        tokens, hidden = _rows(x)
+        norm_out = x if inplace else torch.empty_like(x)
+        res_out = None if residual is None else (residual if inplace else torch.empty_like(residual))
+        C.check(C.lib().b200c_all_reduce_add_rmsnorm(
+            self.ctx, x.data_ptr(), _ptr(residual), _ptr(res_out), norm_out.data_ptr(),
+            gamma.data_ptr(), float(eps), tokens, hidden, DTYPE_CODE[x.dtype], variant, _stream()))
+        return norm_out, res_out
+
+    def all_gather_lastdim(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        rows, cols = _rows(x)
+        if out is None:
+            out = torch.empty(x.shape[:-1] + (cols * self.world,), dtype=x.dtype, device=x.device)
+        C.check(C.lib().b200c_all_gather_lastdim(self.ctx, x.data_ptr(), out.data_ptr(), rows,
+                                                 cols * x.element_size(), _stream()))
+        return out
+
+    def send(self, t: torch.Tensor, dst: int) -> None:
+        nbytes = t.numel() * t.element_size()
+        base = t.data_ptr()
+        for off in range(0, nbytes, self.p2p_bytes):
+            n = min(self.p2p_bytes, nbytes - off)
+            C.check(C.lib().b200c_send(self.ctx, dst, base + off, n, _stream()))
+
+    def recv(self, t: torch.Tensor, src: int) -> torch.Tensor:
+        nbytes = t.numel() * t.element_size()
+        base = t.data_ptr()
+        for off in range(0, nbytes, self.p2p_bytes):
+            n = min(self.p2p_bytes, nbytes - off)
+            C.check(C.lib().b200c_recv(self.ctx, src, base + off, n, _stream()))
+        return t
+
+    def close(self) -> None:
+        if self.ctx:
+            with torch.cuda.device(self.device):
+                C.lib().b200c_destroy(self.ctx)
+                self.ctx = c_void_p(0)
+                for p in self._opened:
+                    C.lib().b200c_close_handle(p)
+                self._opened = []
+                if self._owned_arena:
+                    C.lib().b200c_free_shared(self._owned_arena)
+                    self._owned_arena = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

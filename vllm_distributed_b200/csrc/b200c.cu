@@ -1,0 +1,727 @@
+// b200c.cu -- host side of libb200c.so: context, arena geometry, launch logic and the
+// extern "C" boundary declared in include/b200c.h.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "../../include/b200c.h"
+#include "b200c_kernels.cuh"
+
+using namespace b200c;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t e_ = (expr);                                                            \
+    if (e_ != cudaSuccess)                                                              \
+      return fail(B200C_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), \
+                  __FILE__, __LINE__);                                                  \
+  } while (0)
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+ArenaGeom make_geom(int world, size_t max_bytes, size_t ag_bytes, size_t p2p_bytes,
+                    size_t* total) {
+  ArenaGeom g;
+  const size_t half = align_up(std::max<size_t>(max_bytes, 16), 256);
+  g.hi_off = half;
+  g.lam_stride = 2 * half;
+  g.ag_off = kCtrlBytes + 3 * g.lam_stride;
+  g.ag_stride = align_up(std::max<size_t>(ag_bytes, 16), 256);
+  g.p2p_off = g.ag_off + 2 * g.ag_stride;
+  g.p2p_stride = align_up(std::max<size_t>(p2p_bytes, 16), 256);
+  if (total) *total = g.p2p_off + (size_t)world * 2 * g.p2p_stride;
+  return g;
+}
+
+}  // namespace
+
+struct b200c_ctx {
+  int rank = 0, world = 1, device = 0;
+  char* arena[kMaxRanks] = {};
+  size_t max_bytes = 0, ag_bytes = 0, p2p_bytes = 0;
+  ArenaGeom geom{};
+  LocalState* st = nullptr;
+  int sm_count = 148;
+  // tuning
+  long long oneshot_max_bytes = 256 * 1024;
+  int oneshot_blocks = 148;
+  int twoshot_blocks = 148;
+  int copy_blocks = 64;
+  long long spin_timeout_ms = 10000;
+};
+
+namespace {
+
+int dtype_size(int dtype) {
+  switch (dtype) {
+    case B200C_BF16:
+    case B200C_F16: return 2;
+    case B200C_F32: return 4;
+    default: return 0;
+  }
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+void fill_rank_params(const b200c_ctx* c, RankParams& p) {
+  memset(&p, 0, sizeof(p));
+  for (int r = 0; r < kMaxRanks; ++r) p.arena[r] = c->arena[r];
+  p.st = c->st;
+  p.g = c->geom;
+  p.rank = c->rank;
+  p.world = c->world;
+  p.timeout_ns = (unsigned long long)c->spin_timeout_ms * 1000000ull;
+}
+
+void fill_copy_params(const b200c_ctx* c, CopyParams& p) {
+  memset(&p, 0, sizeof(p));
+  for (int r = 0; r < kMaxRanks; ++r) p.arena[r] = c->arena[r];
+  p.st = c->st;
+  p.g = c->geom;
+  p.rank = c->rank;
+  p.world = c->world;
+  p.timeout_ns = (unsigned long long)c->spin_timeout_ms * 1000000ull;
+}
+
+// Every CTA of a collective kernel must be resident at once (CTAs wait on peers' CTAs).
+template <typename K>
+int coresident_blocks(K kernel, int threads, int sm_count, int* out) {
+  int per_sm = 0;
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
+  if (per_sm < 1) return fail(B200C_ECUDA, "kernel cannot be resident with %d threads", threads);
+  *out = per_sm * sm_count;
+  return B200C_OK;
+}
+
+template <typename K, typename P>
+int launch(K kernel, dim3 grid, int threads, const P& params, cudaStream_t s, bool cooperative) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(threads, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  if (cooperative) {
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, params));
+  return B200C_OK;
+}
+
+// rows are split over `threads` lanes holding up to VPT vectors each
+void norm_shape(int hv, int* vpt, int* threads) {
+  int v = 1;
+  while (v < 4 && (hv + v - 1) / v > 512) v *= 2;
+  int t = (hv + v - 1) / v;
+  t = std::max(32, (t + 31) / 32 * 32);
+  *vpt = v;
+  *threads = t;
+}
+
+int pick_variant(const b200c_ctx* c, size_t bytes, int variant) {
+  if (variant == B200C_ONESHOT || variant == B200C_TWOSHOT) return variant;
+  return ((long long)bytes <= c->oneshot_max_bytes) ? B200C_ONESHOT : B200C_TWOSHOT;
+}
+
+int check_ar_fit(const b200c_ctx* c, size_t bytes, int variant) {
+  if (bytes > c->max_bytes)
+    return fail(B200C_ETOOBIG, "message of %zu bytes exceeds the arena's max_bytes %zu", bytes,
+                c->max_bytes);
+  if (variant == B200C_ONESHOT && bytes * (size_t)c->world > c->geom.lam_stride)
+    return fail(B200C_ETOOBIG, "one-shot needs world*bytes = %zu <= %zu", bytes * c->world,
+                c->geom.lam_stride);
+  if (variant == B200C_TWOSHOT) {
+    const size_t nvec = bytes / 16, chunk = (nvec + c->world - 1) / c->world;
+    if (chunk * 16 * c->world > c->geom.hi_off)
+      return fail(B200C_ETOOBIG, "two-shot scatter area too small for %zu bytes", bytes);
+  }
+  return B200C_OK;
+}
+
+// ---- fused AR + norm dispatch ------------------------------------------------------------------------
+
+template <typename T, int VPT, bool TWOSHOT>
+int launch_ar_norm_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int threads,
+                     int want_blocks, cudaStream_t s) {
+  if (nemu == 0) {
+    int cap = 0;
+    int rc = coresident_blocks(ar_norm_kernel<T, VPT, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
+    if (rc) return rc;
+    const int g = std::max(1, std::min(want_blocks, cap));
+    return launch(ar_norm_kernel<T, VPT, TWOSHOT>, dim3(g, 1, 1), threads, rp[0], s, false);
+  }
+  int cap = 0;
+  int rc = coresident_blocks(ar_norm_kernel_emu<T, VPT, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
+  if (rc) return rc;
+  const int g = std::max(1, std::min(want_blocks, cap / nemu));
+  EmuParams ep;
+  memset(&ep, 0, sizeof(ep));
+  for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
+  return launch(ar_norm_kernel_emu<T, VPT, TWOSHOT>, dim3(g, nemu, 1), threads, ep, s, true);
+}
+
+template <typename T>
+int launch_ar_norm_v(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int vpt, int threads,
+                     bool twoshot, int want_blocks, cudaStream_t s) {
+#define B200C_CASE(V)                                                                      \
+  case V:                                                                                  \
+    return twoshot ? launch_ar_norm_t<T, V, true>(ctxs, nemu, rp, threads, want_blocks, s) \
+                   : launch_ar_norm_t<T, V, false>(ctxs, nemu, rp, threads, want_blocks, s);
+  switch (vpt) {
+    B200C_CASE(1)
+    B200C_CASE(2)
+    B200C_CASE(4)
+  }
+#undef B200C_CASE
+  return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
+}
+
+template <typename T, bool TWOSHOT>
+int launch_ar_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int want_blocks,
+                cudaStream_t s) {
+  const int threads = 512;
+  if (nemu == 0) {
+    int cap = 0;
+    int rc = coresident_blocks(ar_kernel<T, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
+    if (rc) return rc;
+    const int g = std::max(1, std::min(want_blocks, cap));
+    return launch(ar_kernel<T, TWOSHOT>, dim3(g, 1, 1), threads, rp[0], s, false);
+  }
+  int cap = 0;
+  int rc = coresident_blocks(ar_kernel_emu<T, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
+  if (rc) return rc;
+  const int g = std::max(1, std::min(want_blocks, cap / nemu));
+  EmuParams ep;
+  memset(&ep, 0, sizeof(ep));
+  for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
+  return launch(ar_kernel_emu<T, TWOSHOT>, dim3(g, nemu, 1), threads, ep, s, true);
+}
+
+template <typename T>
+int launch_norm_only(const RankParams& rp, int vpt, int threads, int sm_count, cudaStream_t s) {
+  const int g = std::max(1, std::min(rp.tokens, sm_count * 16));
+  switch (vpt) {
+    case 1: return launch(norm_kernel<T, 1>, dim3(g, 1, 1), threads, rp, s, false);
+    case 2: return launch(norm_kernel<T, 2>, dim3(g, 1, 1), threads, rp, s, false);
+    case 4: return launch(norm_kernel<T, 4>, dim3(g, 1, 1), threads, rp, s, false);
+  }
+  return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
+}
+
+int norm_only(RankParams& rp, int dtype, int sm_count, cudaStream_t s) {
+  int vpt, threads;
+  norm_shape(rp.hv, &vpt, &threads);
+  switch (dtype) {
+    case B200C_BF16: return launch_norm_only<__nv_bfloat16>(rp, vpt, threads, sm_count, s);
+    case B200C_F16: return launch_norm_only<__half>(rp, vpt, threads, sm_count, s);
+    case B200C_F32: return launch_norm_only<float>(rp, vpt, threads, sm_count, s);
+  }
+  return fail(B200C_EINVAL, "bad dtype %d", dtype);
+}
+
+int check_rows(int tokens, int hidden, int dtype, int* hv) {
+  const int es = dtype_size(dtype);
+  if (!es) return fail(B200C_EINVAL, "bad dtype %d", dtype);
+  if (tokens < 0 || hidden <= 0) return fail(B200C_EINVAL, "bad shape [%d, %d]", tokens, hidden);
+  if (((size_t)hidden * es) % 16) return fail(B200C_EINVAL, "hidden*sizeof(T) must be a multiple of 16");
+  *hv = (int)((size_t)hidden * es / 16);
+  if (*hv > 4 * 512) return fail(B200C_EINVAL, "hidden %d too large for the fused row kernel", hidden);
+  return B200C_OK;
+}
+
+int sm_count_of_current_device(int* dev, int* sms) {
+  CUDA_TRY(cudaGetDevice(dev));
+  CUDA_TRY(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, *dev));
+  return B200C_OK;
+}
+
+// shared implementation of the real (nemu == 0) and emulated fused entry points
+int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
+                 const void* const* res_ins, void* const* res_outs, void* const* norm_outs,
+                 const void* gamma, float eps, int tokens, int hidden, int dtype, int variant,
+                 cudaStream_t s) {
+  b200c_ctx* c0 = ctxs[0];
+  int hv = 0;
+  int rc = check_rows(tokens, hidden, dtype, &hv);
+  if (rc) return rc;
+  if (tokens == 0) return B200C_OK;
+  const int n = nemu ? nemu : 1;
+  RankParams rp[kMaxRanks];
+  for (int r = 0; r < n; ++r) {
+    if (!ins[r] || !norm_outs[r] || !gamma || !aligned16(ins[r]) || !aligned16(norm_outs[r]) ||
+        !aligned16(gamma) || !aligned16(res_ins[r]) || !aligned16(res_outs[r]))
+      return fail(B200C_EINVAL, "null or misaligned pointer");
+    if ((res_ins[r] == nullptr) != (res_outs[r] == nullptr))
+      return fail(B200C_EINVAL, "residual_in and residual_out must both be given or both be NULL");
+    fill_rank_params(ctxs[r], rp[r]);
+    rp[r].in = ins[r];
+    rp[r].res_in = res_ins[r];
+    rp[r].res_out = res_outs[r];
+    rp[r].norm_out = norm_outs[r];
+    rp[r].gamma = gamma;
+    rp[r].eps = eps;
+    rp[r].tokens = tokens;
+    rp[r].hv = hv;
+    rp[r].hidden = hidden;
+    rp[r].nvec = (unsigned long long)tokens * hv;
+  }
+  if (c0->world == 1) return norm_only(rp[0], dtype, c0->sm_count, s);
+
+  const size_t bytes = (size_t)tokens * hv * 16;
+  variant = pick_variant(c0, bytes, variant);
+  rc = check_ar_fit(c0, bytes, variant);
+  if (rc) return rc;
+  int vpt, threads;
+  norm_shape(hv, &vpt, &threads);
+  const bool two = variant == B200C_TWOSHOT;
+  const int want = two ? c0->twoshot_blocks : std::min(tokens, c0->oneshot_blocks);
+  switch (dtype) {
+    case B200C_BF16: return launch_ar_norm_v<__nv_bfloat16>(ctxs, nemu, rp, vpt, threads, two, want, s);
+    case B200C_F16: return launch_ar_norm_v<__half>(ctxs, nemu, rp, vpt, threads, two, want, s);
+    case B200C_F32: return launch_ar_norm_v<float>(ctxs, nemu, rp, vpt, threads, two, want, s);
+  }
+  return fail(B200C_EINVAL, "bad dtype %d", dtype);
+}
+
+int ar_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins, void* const* outs,
+            size_t numel, int dtype, int variant, cudaStream_t s) {
+  b200c_ctx* c0 = ctxs[0];
+  const int es = dtype_size(dtype);
+  if (!es) return fail(B200C_EINVAL, "bad dtype %d", dtype);
+  const size_t bytes = numel * es;
+  if (bytes % 16) return fail(B200C_EINVAL, "numel*sizeof(T) = %zu is not a multiple of 16", bytes);
+  if (bytes == 0) return B200C_OK;
+  const int n = nemu ? nemu : 1;
+  RankParams rp[kMaxRanks];
+  for (int r = 0; r < n; ++r) {
+    if (!ins[r] || !outs[r] || !aligned16(ins[r]) || !aligned16(outs[r]))
+      return fail(B200C_EINVAL, "null or misaligned pointer");
+    fill_rank_params(ctxs[r], rp[r]);
+    rp[r].in = ins[r];
+    rp[r].out = outs[r];
+    rp[r].nvec = bytes / 16;
+  }
+  if (c0->world == 1) {
+    if (ins[0] != outs[0])
+      CUDA_TRY(cudaMemcpyAsync(outs[0], ins[0], bytes, cudaMemcpyDeviceToDevice, s));
+    return B200C_OK;
+  }
+  variant = pick_variant(c0, bytes, variant);
+  int rc = check_ar_fit(c0, bytes, variant);
+  if (rc) return rc;
+  const bool two = variant == B200C_TWOSHOT;
+  const size_t nvec = bytes / 16;
+  int want = two ? c0->twoshot_blocks : c0->oneshot_blocks;
+  want = (int)std::min<size_t>((size_t)want, (nvec + 511) / 512);
+#define B200C_AR(T) \
+  (two ? launch_ar_t<T, true>(ctxs, nemu, rp, want, s) : launch_ar_t<T, false>(ctxs, nemu, rp, want, s))
+  switch (dtype) {
+    case B200C_BF16: return B200C_AR(__nv_bfloat16);
+    case B200C_F16: return B200C_AR(__half);
+    case B200C_F32: return B200C_AR(float);
+  }
+#undef B200C_AR
+  return fail(B200C_EINVAL, "bad dtype %d", dtype);
+}
+
+int check_emu(b200c_ctx* const* ctxs, int world) {
+  if (!ctxs || world < 2 || world > kMaxRanks) return fail(B200C_EINVAL, "bad emulated world %d", world);
+  for (int r = 0; r < world; ++r)
+    if (!ctxs[r] || ctxs[r]->world != world || ctxs[r]->rank != r)
+      return fail(B200C_EINVAL, "ctxs[%d] is not rank %d of a %d-rank group", r, r, world);
+  return B200C_OK;
+}
+
+int copy_grid(const b200c_ctx* c, size_t nvec, int nemu, void* kernel_fn, int* g) {
+  int per_sm = 0;
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel_fn, 512, 0));
+  int cap = std::max(1, per_sm * c->sm_count / std::max(1, nemu));
+  size_t want = std::min<size_t>((size_t)c->copy_blocks, (nvec + 511) / 512);
+  *g = (int)std::max<size_t>(1, std::min<size_t>(want, (size_t)cap));
+  return B200C_OK;
+}
+
+}  // namespace
+
+// ================================ extern "C" =========================================================
+
+extern "C" {
+
+int b200c_version(void) { return 1; }
+
+const char* b200c_last_error(void) { return g_err; }
+
+int b200c_arena_bytes(int world, size_t max_bytes, size_t ag_bytes, size_t p2p_bytes,
+                      size_t* out_bytes) {
+  if (world < 1 || world > kMaxRanks || !out_bytes) return fail(B200C_EINVAL, "bad world %d", world);
+  make_geom(world, max_bytes, ag_bytes, p2p_bytes, out_bytes);
+  return B200C_OK;
+}
+
+int b200c_alloc_shared(size_t bytes, void** dptr, uint8_t handle[B200C_IPC_HANDLE_BYTES]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200C_IPC_HANDLE_BYTES, "IPC handle size");
+  if (!dptr || !bytes) return fail(B200C_EINVAL, "bad arguments");
+  CUDA_TRY(cudaMalloc(dptr, bytes));
+  if (handle) {
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, *dptr);
+    if (e != cudaSuccess) {
+      cudaFree(*dptr);
+      *dptr = nullptr;
+      return fail(B200C_ECUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+    }
+    memcpy(handle, &h, sizeof(h));
+  }
+  return B200C_OK;
+}
+
+int b200c_open_handle(const uint8_t handle[B200C_IPC_HANDLE_BYTES], void** dptr) {
+  if (!handle || !dptr) return fail(B200C_EINVAL, "bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  CUDA_TRY(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return B200C_OK;
+}
+
+int b200c_close_handle(void* dptr) {
+  if (!dptr) return B200C_OK;
+  CUDA_TRY(cudaIpcCloseMemHandle(dptr));
+  return B200C_OK;
+}
+
+int b200c_free_shared(void* dptr) {
+  if (!dptr) return B200C_OK;
+  CUDA_TRY(cudaFree(dptr));
+  return B200C_OK;
+}
+
+int b200c_init(int rank, int world, void* const* arena_ptrs, size_t max_bytes, size_t ag_bytes,
+               size_t p2p_bytes, b200c_ctx** out) {
+  if (!out) return fail(B200C_EINVAL, "ctx out pointer is NULL");
+  if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world)
+    return fail(B200C_EINVAL, "bad rank %d / world %d (1..%d ranks)", rank, world, kMaxRanks);
+  if (world > 1) {
+    if (!arena_ptrs) return fail(B200C_EINVAL, "arena_ptrs is NULL");
+    for (int r = 0; r < world; ++r)
+      if (!arena_ptrs[r] || !aligned16(arena_ptrs[r]))
+        return fail(B200C_EINVAL, "arena_ptrs[%d] is NULL or misaligned", r);
+    if (max_bytes % 16 || ag_bytes % 16 || p2p_bytes % 16)
+      return fail(B200C_EINVAL, "arena sizes must be multiples of 16");
+  }
+  b200c_ctx* c = new (std::nothrow) b200c_ctx();
+  if (!c) return fail(B200C_ENOMEM, "out of host memory");
+  c->rank = rank;
+  c->world = world;
+  int rc = sm_count_of_current_device(&c->device, &c->sm_count);
+  if (rc) {
+    delete c;
+    return rc;
+  }
+  c->oneshot_blocks = c->sm_count;
+  c->twoshot_blocks = c->sm_count;
+  if (world > 1) {
+    c->max_bytes = max_bytes;
+    c->ag_bytes = ag_bytes;
+    c->p2p_bytes = p2p_bytes;
+    size_t total = 0;
+    c->geom = make_geom(world, max_bytes, ag_bytes, p2p_bytes, &total);
+    for (int r = 0; r < world; ++r) c->arena[r] = static_cast<char*>(arena_ptrs[r]);
+    cudaError_t e = cudaMalloc(&c->st, sizeof(LocalState));
+    if (e == cudaSuccess) e = cudaMemset(c->st, 0, sizeof(LocalState));
+    // own arena: flags to zero, receive regions to "not arrived"
+    if (e == cudaSuccess) e = cudaMemset(c->arena[rank], 0, kCtrlBytes);
+    if (e == cudaSuccess) {
+      const size_t nvec = 3 * c->geom.lam_stride / 16;
+      fill_not_arrived_kernel<<<c->sm_count * 4, 256>>>(
+          reinterpret_cast<uint4*>(c->arena[rank] + kCtrlBytes), nvec);
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+      if (c->st) cudaFree(c->st);
+      delete c;
+      return fail(B200C_ECUDA, "b200c_init: %s", cudaGetErrorString(e));
+    }
+  }
+  *out = c;
+  return B200C_OK;
+}
+
+int b200c_destroy(b200c_ctx* c) {
+  if (!c) return B200C_OK;
+  if (c->st) {
+    cudaDeviceSynchronize();
+    cudaFree(c->st);
+  }
+  delete c;
+  return B200C_OK;
+}
+
+int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  switch (key) {
+    case B200C_TUNE_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = v; break;
+    case B200C_TUNE_ONESHOT_BLOCKS: c->oneshot_blocks = (int)std::max<long long>(1, v); break;
+    case B200C_TUNE_TWOSHOT_BLOCKS: c->twoshot_blocks = (int)std::max<long long>(1, v); break;
+    case B200C_TUNE_SPIN_TIMEOUT_MS: c->spin_timeout_ms = std::max<long long>(0, v); break;
+    case B200C_TUNE_COPY_BLOCKS: c->copy_blocks = (int)std::max<long long>(1, v); break;
+    default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
+  }
+  return B200C_OK;
+}
+
+int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
+  if (!c || !v) return fail(B200C_EINVAL, "bad arguments");
+  switch (key) {
+    case B200C_TUNE_ONESHOT_MAX_BYTES: *v = c->oneshot_max_bytes; break;
+    case B200C_TUNE_ONESHOT_BLOCKS: *v = c->oneshot_blocks; break;
+    case B200C_TUNE_TWOSHOT_BLOCKS: *v = c->twoshot_blocks; break;
+    case B200C_TUNE_SPIN_TIMEOUT_MS: *v = c->spin_timeout_ms; break;
+    case B200C_TUNE_COPY_BLOCKS: *v = c->copy_blocks; break;
+    default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
+  }
+  return B200C_OK;
+}
+
+int b200c_query_error(b200c_ctx* c) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  if (!c->st) return B200C_OK;
+  uint32_t e = 0;
+  CUDA_TRY(cudaMemcpy(&e, &c->st->error, sizeof(e), cudaMemcpyDeviceToHost));
+  if (e) return fail(B200C_ETIMEOUT, "a device-side wait on a peer timed out (rank %d)", c->rank);
+  return B200C_OK;
+}
+
+int b200c_all_reduce(b200c_ctx* c, const void* in, void* out, size_t numel, int dtype, int variant,
+                     void* stream) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  b200c_ctx* ctxs[1] = {c};
+  const void* ins[1] = {in};
+  void* outs[1] = {out};
+  return ar_impl(ctxs, 0, ins, outs, numel, dtype, variant, static_cast<cudaStream_t>(stream));
+}
+
+int b200c_all_reduce_add_rmsnorm(b200c_ctx* c, const void* in, const void* residual_in,
+                                 void* residual_out, void* norm_out, const void* gamma, float eps,
+                                 int tokens, int hidden, int dtype, int variant, void* stream) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  b200c_ctx* ctxs[1] = {c};
+  const void* ins[1] = {in};
+  const void* ri[1] = {residual_in};
+  void* ro[1] = {residual_out};
+  void* no[1] = {norm_out};
+  return ar_norm_impl(ctxs, 0, ins, ri, ro, no, gamma, eps, tokens, hidden, dtype, variant,
+                      static_cast<cudaStream_t>(stream));
+}
+
+static int local_norm(void* out, const void* x, const void* res_in, void* res_out,
+                      const void* gamma, float eps, int tokens, int hidden, int dtype,
+                      void* stream) {
+  int hv = 0;
+  int rc = check_rows(tokens, hidden, dtype, &hv);
+  if (rc) return rc;
+  if (tokens == 0) return B200C_OK;
+  if (!out || !x || !gamma || !aligned16(out) || !aligned16(x) || !aligned16(gamma) ||
+      !aligned16(res_in) || !aligned16(res_out))
+    return fail(B200C_EINVAL, "null or misaligned pointer");
+  int dev = 0, sms = 0;
+  rc = sm_count_of_current_device(&dev, &sms);
+  if (rc) return rc;
+  RankParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.world = 1;
+  rp.in = x;
+  rp.res_in = res_in;
+  rp.res_out = res_out;
+  rp.norm_out = out;
+  rp.gamma = gamma;
+  rp.eps = eps;
+  rp.tokens = tokens;
+  rp.hv = hv;
+  rp.hidden = hidden;
+  rp.nvec = (unsigned long long)tokens * hv;
+  return norm_only(rp, dtype, sms, static_cast<cudaStream_t>(stream));
+}
+
+int b200c_fused_add_rms_norm(void* x_inout, void* residual_inout, const void* gamma, float eps,
+                             int tokens, int hidden, int dtype, void* stream) {
+  if (!residual_inout) return fail(B200C_EINVAL, "residual is NULL");
+  return local_norm(x_inout, x_inout, residual_inout, residual_inout, gamma, eps, tokens, hidden,
+                    dtype, stream);
+}
+
+int b200c_rms_norm(void* out, const void* x, const void* gamma, float eps, int tokens, int hidden,
+                   int dtype, void* stream) {
+  return local_norm(out, x, nullptr, nullptr, gamma, eps, tokens, hidden, dtype, stream);
+}
+
+static int all_gather_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
+                           void* const* outs, int rows, size_t row_bytes, cudaStream_t s) {
+  b200c_ctx* c0 = ctxs[0];
+  if (rows < 0 || row_bytes % 16) return fail(B200C_EINVAL, "row_bytes must be a multiple of 16");
+  if (rows == 0 || row_bytes == 0) return B200C_OK;
+  const size_t out_bytes = (size_t)rows * row_bytes * c0->world;
+  const int n = nemu ? nemu : 1;
+  for (int r = 0; r < n; ++r)
+    if (!ins[r] || !outs[r] || !aligned16(ins[r]) || !aligned16(outs[r]))
+      return fail(B200C_EINVAL, "null or misaligned pointer");
+  if (c0->world == 1) {
+    if (ins[0] != outs[0])
+      CUDA_TRY(cudaMemcpyAsync(outs[0], ins[0], out_bytes, cudaMemcpyDeviceToDevice, s));
+    return B200C_OK;
+  }
+  if (out_bytes > c0->ag_bytes)
+    return fail(B200C_ETOOBIG, "all-gather output of %zu bytes exceeds ag_bytes %zu", out_bytes,
+                c0->ag_bytes);
+  const size_t slab_vecs = (size_t)rows * row_bytes / 16;
+  CopyParams cp[kMaxRanks];
+  for (int r = 0; r < n; ++r) {
+    fill_copy_params(ctxs[r], cp[r]);
+    cp[r].in = ins[r];
+    cp[r].out = outs[r];
+    cp[r].rows = rows;
+    cp[r].row_vecs = row_bytes / 16;
+  }
+  int g = 1;
+  if (nemu == 0) {
+    int rc = copy_grid(c0, slab_vecs, 0, (void*)all_gather_kernel, &g);
+    if (rc) return rc;
+    return launch(all_gather_kernel, dim3(g, 1, 1), 512, cp[0], s, false);
+  }
+  int rc = copy_grid(c0, slab_vecs, nemu, (void*)all_gather_kernel_emu, &g);
+  if (rc) return rc;
+  EmuCopyParams ep;
+  memset(&ep, 0, sizeof(ep));
+  for (int r = 0; r < nemu; ++r) ep.r[r] = cp[r];
+  return launch(all_gather_kernel_emu, dim3(g, nemu, 1), 512, ep, s, true);
+}
+
+int b200c_all_gather_lastdim(b200c_ctx* c, const void* in, void* out, int rows, size_t row_bytes,
+                             void* stream) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  b200c_ctx* ctxs[1] = {c};
+  const void* ins[1] = {in};
+  void* outs[1] = {out};
+  return all_gather_impl(ctxs, 0, ins, outs, rows, row_bytes, static_cast<cudaStream_t>(stream));
+}
+
+static int p2p_check(b200c_ctx* c, int peer, const void* buf, size_t bytes) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  if (c->world < 2) return fail(B200C_EINVAL, "send/recv need a group of at least 2 ranks");
+  if (peer < 0 || peer >= c->world || peer == c->rank) return fail(B200C_EINVAL, "bad peer %d", peer);
+  if (bytes % 16 || !buf || !aligned16(buf)) return fail(B200C_EINVAL, "buffer must be 16-byte aligned and sized");
+  if (bytes > c->p2p_bytes)
+    return fail(B200C_ETOOBIG, "message of %zu bytes exceeds p2p_bytes %zu", bytes, c->p2p_bytes);
+  return B200C_OK;
+}
+
+int b200c_send(b200c_ctx* c, int dst, const void* buf, size_t bytes, void* stream) {
+  int rc = p2p_check(c, dst, buf, bytes);
+  if (rc) return rc;
+  if (bytes == 0) return B200C_OK;
+  CopyParams cp;
+  fill_copy_params(c, cp);
+  cp.in = buf;
+  cp.peer = dst;
+  cp.nvec = bytes / 16;
+  int g = 1;
+  rc = copy_grid(c, cp.nvec, 0, (void*)send_kernel, &g);
+  if (rc) return rc;
+  return launch(send_kernel, dim3(g, 1, 1), 512, cp, static_cast<cudaStream_t>(stream), false);
+}
+
+int b200c_recv(b200c_ctx* c, int src, void* buf, size_t bytes, void* stream) {
+  int rc = p2p_check(c, src, buf, bytes);
+  if (rc) return rc;
+  if (bytes == 0) return B200C_OK;
+  CopyParams cp;
+  fill_copy_params(c, cp);
+  cp.out = buf;
+  cp.peer = src;
+  cp.nvec = bytes / 16;
+  int g = 1;
+  rc = copy_grid(c, cp.nvec, 0, (void*)recv_kernel, &g);
+  if (rc) return rc;
+  return launch(recv_kernel, dim3(g, 1, 1), 512, cp, static_cast<cudaStream_t>(stream), false);
+}
+
+// ---- single-GPU rank emulation ----------------------------------------------------------------------
+
+int b200c_emu_all_reduce(b200c_ctx* const* ctxs, int world, const void* const* ins,
+                         void* const* outs, size_t numel, int dtype, int variant, void* stream) {
+  int rc = check_emu(ctxs, world);
+  if (rc) return rc;
+  if (!ins || !outs) return fail(B200C_EINVAL, "null pointer array");
+  return ar_impl(ctxs, world, ins, outs, numel, dtype, variant, static_cast<cudaStream_t>(stream));
+}
+
+int b200c_emu_all_reduce_add_rmsnorm(b200c_ctx* const* ctxs, int world, const void* const* ins,
+                                     const void* const* residual_ins, void* const* residual_outs,
+                                     void* const* norm_outs, const void* gamma, float eps,
+                                     int tokens, int hidden, int dtype, int variant, void* stream) {
+  int rc = check_emu(ctxs, world);
+  if (rc) return rc;
+  if (!ins || !residual_ins || !residual_outs || !norm_outs)
+    return fail(B200C_EINVAL, "null pointer array");
+  return ar_norm_impl(ctxs, world, ins, residual_ins, residual_outs, norm_outs, gamma, eps, tokens,
+                      hidden, dtype, variant, static_cast<cudaStream_t>(stream));
+}
+
+int b200c_emu_all_gather_lastdim(b200c_ctx* const* ctxs, int world, const void* const* ins,
+                                 void* const* outs, int rows, size_t row_bytes, void* stream) {
+  int rc = check_emu(ctxs, world);
+  if (rc) return rc;
+  if (!ins || !outs) return fail(B200C_EINVAL, "null pointer array");
+  return all_gather_impl(ctxs, world, ins, outs, rows, row_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200c_emu_sendrecv(b200c_ctx* const* ctxs, int world, int src, int dst, const void* sendbuf,
+                       void* recvbuf, size_t bytes, void* stream) {
+  int rc = check_emu(ctxs, world);
+  if (rc) return rc;
+  if (src < 0 || src >= world || dst < 0 || dst >= world || src == dst)
+    return fail(B200C_EINVAL, "bad src %d / dst %d", src, dst);
+  rc = p2p_check(ctxs[src], dst, sendbuf, bytes);
+  if (rc) return rc;
+  rc = p2p_check(ctxs[dst], src, recvbuf, bytes);
+  if (rc) return rc;
+  if (bytes == 0) return B200C_OK;
+  EmuCopyParams ep;
+  memset(&ep, 0, sizeof(ep));
+  fill_copy_params(ctxs[src], ep.r[0]);
+  ep.r[0].in = sendbuf;
+  ep.r[0].peer = dst;
+  ep.r[0].nvec = bytes / 16;
+  ep.r[0].role = 0;
+  fill_copy_params(ctxs[dst], ep.r[1]);
+  ep.r[1].out = recvbuf;
+  ep.r[1].peer = src;
+  ep.r[1].nvec = bytes / 16;
+  ep.r[1].role = 1;
+  int g = 1;
+  rc = copy_grid(ctxs[src], bytes / 16, 2, (void*)sendrecv_kernel_emu, &g);
+  if (rc) return rc;
+  return launch(sendrecv_kernel_emu, dim3(g, 2, 1), 512, ep, static_cast<cudaStream_t>(stream), true);
+}
+
+}  // extern "C"

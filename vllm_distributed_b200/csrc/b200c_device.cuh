@@ -1,0 +1,217 @@
+// b200c_device.cuh -- device-side building blocks for the B200 (sm_100a) TP hot path.
+//
+// Memory-system facts this code is written around (B200, NVLink 5 / NVSwitch):
+//   * peer stores are posted (fire-and-forget) while peer loads pay a full fabric round
+//     trip (~1.8k cycles), so every exchange here is a PUSH: a rank reads its own input
+//     from local HBM and writes into the peers' arenas;
+//   * peer data bypasses the local L2, and L1 is not coherent, so every wait loop polls
+//     with ld.volatile (L1 bypass) on LOCAL memory that a peer writes;
+//   * the data word itself is the arrival flag (a 32-bit "not arrived" pattern that the
+//     payload can never contain), so the all-reduce needs no fence and no barrier.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace b200c {
+
+constexpr int kMaxRanks = 8;
+// A 32-bit word that marks "not arrived yet".  For fp32 it is -0.0f; for the 16-bit
+// types it is the aligned pair (+0.0, -0.0).  Payload words equal to it are rewritten to
+// +0.0 before they are pushed (numerically the same value), so a receiver can never
+// mistake data for the marker.  PTX models a vector access as independent accesses of
+// its element type, so a .b32 element never tears.
+constexpr uint32_t kNotArrived = 0x80000000u;
+
+// ---- raw memory operations -----------------------------------------------------------
+
+__device__ __forceinline__ uint4 ld_poll_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+// Streaming read of data nobody writes during the kernel (inputs, residual, gamma).
+__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ uint4 ld_v4(const void* p) {
+  return *reinterpret_cast<const uint4*>(p);
+}
+
+// Push to a (possibly remote) arena.  volatile keeps the store where it is written and
+// stops the compiler from merging or eliding it; no ordering is needed (data == flag).
+__device__ __forceinline__ void st_push_v4(void* p, const uint4& v) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void st_v4(void* p, const uint4& v) {
+  *reinterpret_cast<uint4*>(p) = v;
+}
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// ---- arrival marker helpers ----------------------------------------------------------------
+
+__device__ __forceinline__ bool not_arrived(const uint4& v) {
+  return (v.x == kNotArrived) | (v.y == kNotArrived) | (v.z == kNotArrived) |
+         (v.w == kNotArrived);
+}
+
+__device__ __forceinline__ void scrub(uint4& v) {
+  v.x = (v.x == kNotArrived) ? 0u : v.x;
+  v.y = (v.y == kNotArrived) ? 0u : v.y;
+  v.z = (v.z == kNotArrived) ? 0u : v.z;
+  v.w = (v.w == kNotArrived) ? 0u : v.w;
+}
+
+// ---- bounded waiting ----------------------------------------------------------------------------
+// A wait on a peer never spins forever: after timeout_ns (0 = unbounded) the sticky error
+// word is set and every later wait in this and following kernels falls through at once.
+struct SpinGuard {
+  uint32_t iters = 0;
+  unsigned long long t0 = 0;
+  // returns true when the caller must give up
+  __device__ __forceinline__ bool expired(unsigned long long timeout_ns, uint32_t* err) {
+    if ((++iters & 0x3ffu) != 0) return false;
+    if (ld_volatile_u32(err) != 0) return true;
+    if (timeout_ns == 0) return false;
+    unsigned long long now = globaltimer_ns();
+    if (t0 == 0) {
+      t0 = now;
+      return false;
+    }
+    if (now - t0 > timeout_ns) {
+      atomicExch(err, 1u);
+      return true;
+    }
+    return false;
+  }
+};
+
+// ---- element types ---------------------------------------------------------------------------------
+
+template <typename T>
+struct VecOps;
+
+template <>
+struct VecOps<__nv_bfloat16> {
+  static constexpr int EPV = 8;  // elements per 16-byte vector
+  static __device__ __forceinline__ void to_float(const uint4& v, float (&f)[8]) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      f[2 * i] = __uint_as_float(w[i] << 16);
+      f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  static __device__ __forceinline__ uint4 from_float(const float (&f)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  // round an fp32 value to T and back (the x.to(weight.dtype) step of the norm)
+  static __device__ __forceinline__ float round_trip(float x) {
+    return __bfloat162float(__float2bfloat16_rn(x));
+  }
+};
+
+template <>
+struct VecOps<__half> {
+  static constexpr int EPV = 8;
+  static __device__ __forceinline__ void to_float(const uint4& v, float (&f)[8]) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 p = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      f[2 * i] = p.x;
+      f[2 * i + 1] = p.y;
+    }
+  }
+  static __device__ __forceinline__ uint4 from_float(const float (&f)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  static __device__ __forceinline__ float round_trip(float x) {
+    return __half2float(__float2half_rn(x));
+  }
+};
+
+template <>
+struct VecOps<float> {
+  static constexpr int EPV = 4;
+  static __device__ __forceinline__ void to_float(const uint4& v, float (&f)[4]) {
+    f[0] = __uint_as_float(v.x);
+    f[1] = __uint_as_float(v.y);
+    f[2] = __uint_as_float(v.z);
+    f[3] = __uint_as_float(v.w);
+  }
+  static __device__ __forceinline__ uint4 from_float(const float (&f)[4]) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                      __float_as_uint(f[3]));
+  }
+  static __device__ __forceinline__ float round_trip(float x) { return x; }
+};
+
+// ---- block-wide sum (warp shuffles, one shared-memory hop) -------------------------------------
+// Fixed reduction tree => the same row gives the same bits on every rank.
+__device__ __forceinline__ float block_sum(float v, float* smem /* >= 33 floats */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    float t = (lane < nwarps) ? smem[lane] : 0.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) smem[32] = t;
+  }
+  __syncthreads();
+  float total = smem[32];
+  __syncthreads();  // smem is reused by the next row
+  return total;
+}
+
+}  // namespace b200c

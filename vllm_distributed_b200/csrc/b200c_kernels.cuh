@@ -1,0 +1,563 @@
+// b200c_kernels.cuh -- kernels of the TP hot path (all-reduce [+ residual + RMSNorm],
+// lm_head all-gather, pipeline send/recv).  See DESIGN.md for the protocol proofs.
+#pragma once
+
+#include "b200c_device.cuh"
+
+namespace b200c {
+
+// ---- arena layout (bytes from the arena base; identical on every rank) -----------------------
+constexpr size_t kCtrlBytes = 64 * 1024;
+constexpr size_t kFlagStride = 128;  // one flag per 128-byte line
+constexpr size_t kAgFlagOff = 0;          // [2 parity][8 src]
+constexpr size_t kP2pReadyOff = 4096;     // [8 src][2 slot]   written by the sender
+constexpr size_t kP2pCreditOff = 8192;    // [8 dst][2 slot]   written by the receiver
+
+struct ArenaGeom {
+  size_t lam_stride;  // bytes of one rotating receive region (lo half + hi half)
+  size_t hi_off;      // offset of the hi (gather) half inside a region
+  size_t ag_off;      // offset of all-gather staging [2]
+  size_t ag_stride;
+  size_t p2p_off;     // offset of mailboxes [world src][2 slot]
+  size_t p2p_stride;
+};
+
+// Private (not peer-visible) per-rank device state.  Lives in device memory so that a
+// captured CUDA graph replays correctly: the kernels advance it themselves.
+struct LocalState {
+  uint32_t epoch;        // all-reduce call counter; region = epoch % 3
+  uint32_t arrive;       // CTA arrival counter (end-of-kernel bookkeeping)
+  uint32_t error;        // sticky: 1 = a wait on a peer timed out
+  uint32_t ag_seq;       // all-gather call counter
+  uint32_t ag_arrive_push;
+  uint32_t ag_arrive_done;
+  uint32_t p2p_arrive;
+  uint32_t pad0;
+  unsigned long long dirty_lo[3];  // bytes peers wrote into each region's lo / hi half
+  unsigned long long dirty_hi[3];
+  uint32_t send_seq[kMaxRanks];
+  uint32_t recv_seq[kMaxRanks];
+};
+
+struct RankParams {
+  char* arena[kMaxRanks];  // every rank's arena as mapped in this process
+  LocalState* st;
+  ArenaGeom g;
+  const void* in;
+  void* out;  // plain all-reduce result
+  const void* res_in;
+  void* res_out;
+  void* norm_out;
+  const void* gamma;
+  float eps;
+  int rank, world;
+  int tokens;
+  int hv;                  // 16-byte vectors per row
+  int hidden;              // elements per row
+  unsigned long long nvec;  // total 16-byte vectors
+  unsigned long long timeout_ns;
+};
+
+struct EmuParams {
+  RankParams r[kMaxRanks];
+};
+
+__device__ __forceinline__ char* lam_region(const RankParams& p, int rank, uint32_t b) {
+  return p.arena[rank] + kCtrlBytes + (size_t)b * p.g.lam_stride;
+}
+
+// ---- waiting on pushed data -------------------------------------------------------------------------
+
+// Poll one local vector until the peer's push has landed.
+__device__ __forceinline__ uint4 wait_one(const char* addr, const RankParams& p, SpinGuard& sg) {
+  uint4 v = ld_poll_v4(addr);
+  while (not_arrived(v)) {
+    if (sg.expired(p.timeout_ns, &p.st->error)) break;
+    v = ld_poll_v4(addr);
+  }
+  return v;
+}
+
+// One-shot gather-and-sum of vector `idx`: slot r of my region holds rank r's copy; my own
+// contribution comes straight from `in`.  All world-1 polls are issued back to back so the
+// L2 round trips overlap; accumulation is fp32 in rank order 0..N-1 with one rounding (the
+// reference's packed_reduce order, vllm_custom_all_reduce.cuh:213-221).
+template <typename T>
+__device__ __forceinline__ uint4 gather_sum(const char* my_lo, size_t slot_bytes, size_t idx,
+                                            const uint4& own, const RankParams& p,
+                                            SpinGuard& sg) {
+  constexpr int EPV = VecOps<T>::EPV;
+  uint4 v[kMaxRanks];
+  const char* base = my_lo + idx * 16;
+  bool pending;
+  do {
+    pending = false;
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {
+      if (r < p.world && r != p.rank) v[r] = ld_poll_v4(base + (size_t)r * slot_bytes);
+    }
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {
+      if (r < p.world && r != p.rank) pending |= not_arrived(v[r]);
+    }
+    if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
+  } while (pending);
+
+  float acc[EPV], f[EPV];
+#pragma unroll
+  for (int r = 0; r < kMaxRanks; ++r) {
+    if (r < p.world) {
+      const uint4 x = (r == p.rank) ? own : v[r];
+      if (r == 0) {
+        VecOps<T>::to_float(x, acc);
+      } else {
+        VecOps<T>::to_float(x, f);
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) acc[e] += f[e];
+      }
+    }
+  }
+  return VecOps<T>::from_float(acc);
+}
+
+// Re-arm the region the PREVIOUS call used (nobody can push into it again before this
+// kernel has finished on this rank; see DESIGN.md "rotation").
+__device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size_t gtid,
+                                      size_t gsize) {
+  const uint4 m = make_uint4(kNotArrived, kNotArrived, kNotArrived, kNotArrived);
+  const size_t n = (size_t)(bytes >> 4);
+  for (size_t i = gtid; i < n; i += gsize) st_v4(base + i * 16, m);
+}
+
+// End-of-kernel bookkeeping: the last CTA of this rank publishes the next epoch.
+__device__ __forceinline__ void finish_call(const RankParams& p, uint32_t epoch,
+                                            unsigned long long dlo, unsigned long long dhi) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(&p.st->arrive, 1u);
+    if (prev == gridDim.x - 1) {
+      const uint32_t b = epoch % 3u;
+      p.st->dirty_lo[b] = dlo;
+      p.st->dirty_hi[b] = dhi;
+      p.st->arrive = 0;
+      __threadfence();
+      p.st->epoch = epoch + 1;
+    }
+  }
+}
+
+// ---- row epilogue: residual add + RMSNorm ------------------------------------------------------
+// x[j] holds the T-rounded all-reduce sum for vector (tid + j*blockDim) of the row.
+// VLLM/ir/ops/layernorm.py:39-58.
+template <typename T, int VPT>
+__device__ __forceinline__ void row_epilogue(uint4 (&s)[VPT], size_t row_vec0, const RankParams& p,
+                                             float* smem) {
+  constexpr int EPV = VecOps<T>::EPV;
+  float x[VPT][EPV];
+  float ss = 0.0f;
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int c = threadIdx.x + j * blockDim.x;
+    if (c < p.hv) {
+      VecOps<T>::to_float(s[j], x[j]);
+      if (p.res_in != nullptr) {
+        float r[EPV];
+        const uint4 rv = ld_stream_v4((const char*)p.res_in + (row_vec0 + c) * 16);
+        VecOps<T>::to_float(rv, r);
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) x[j][e] = x[j][e] + r[e];
+        st_v4((char*)p.res_out + (row_vec0 + c) * 16, VecOps<T>::from_float(x[j]));
+      }
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) ss += x[j][e] * x[j][e];
+    }
+  }
+  const float total = block_sum(ss, smem);
+  const float rs = 1.0f / sqrtf(total / (float)p.hidden + p.eps);
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int c = threadIdx.x + j * blockDim.x;
+    if (c < p.hv) {
+      float g[EPV], y[EPV];
+      VecOps<T>::to_float(ld_v4((const char*)p.gamma + (size_t)c * 16), g);
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) y[e] = VecOps<T>::round_trip(x[j][e] * rs) * g[e];
+      st_v4((char*)p.norm_out + (row_vec0 + c) * 16, VecOps<T>::from_float(y));
+    }
+  }
+}
+
+// ---- fused all-reduce + residual + RMSNorm ---------------------------------------------------
+//
+// ONE-SHOT (latency regime): phase A pushes my rows into slot[rank] of every peer's region,
+// phase C polls slot[r] for all r, sums, and runs the epilogue.  One fabric traversal, no
+// barrier.  Link traffic (N-1)*S out per rank.
+//
+// TWO-SHOT (bandwidth regime): phase A pushes vector chunk j of my input to rank j (scatter),
+// phase B reduces my chunk and pushes the T-rounded sums into the hi half of EVERY rank's
+// region (gather), phase C polls the gathered sums row by row and runs the epilogue on all
+// rows (local HBM work, an order of magnitude cheaper than the link).  Link traffic
+// 2*(N-1)/N*S out per rank.  CTAs wait only on data whose producers never wait on them, and
+// the grid is sized to be co-resident, so the kernel cannot deadlock.
+template <typename T, int VPT, bool TWOSHOT>
+__device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
+  const uint32_t epoch = p.st->epoch;
+  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  const size_t nvec = (size_t)p.nvec;
+  const size_t chunk = (nvec + p.world - 1) / p.world;  // two-shot: vectors owned per rank
+  char* my_lo = lam_region(p, p.rank, b);
+  char* my_hi = my_lo + p.g.hi_off;
+  SpinGuard sg;
+
+  // ---- phase A: push
+  if (!TWOSHOT) {
+    const size_t slot_off = (size_t)p.rank * nvec * 16;
+    for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
+#pragma unroll
+      for (int j = 0; j < VPT; ++j) {
+        const int c = threadIdx.x + j * blockDim.x;
+        if (c < p.hv) {
+          const size_t idx = (size_t)row * p.hv + c;
+          uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+          scrub(v);
+#pragma unroll
+          for (int r = 0; r < kMaxRanks; ++r)
+            if (r < p.world && r != p.rank) st_push_v4(lam_region(p, r, b) + slot_off + idx * 16, v);
+        }
+      }
+    }
+  } else {
+    for (size_t idx = gtid; idx < nvec; idx += gsize) {
+      const int owner = (int)(idx / chunk);
+      if (owner != p.rank) {
+        uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+        scrub(v);
+        st_push_v4(lam_region(p, owner, b) + ((size_t)p.rank * chunk + (idx - owner * chunk)) * 16,
+                   v);
+      }
+    }
+  }
+
+  // ---- re-arm the previous call's region while the pushes are in flight
+  {
+    char* prev = lam_region(p, p.rank, pb);
+    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
+    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
+  }
+
+  // ---- phase B (two-shot): reduce my chunk, push the sums to every rank's hi half
+  if (TWOSHOT) {
+    const size_t lo = (size_t)p.rank * chunk;
+    const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+    for (size_t i = lo + gtid; i < hi; i += gsize) {
+      const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
+      uint4 s = gather_sum<T>(my_lo, chunk * 16, i - lo, own, p, sg);
+      scrub(s);
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
+    }
+  }
+
+  // ---- phase C: rows
+  for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
+    const size_t row_vec0 = (size_t)row * p.hv;
+    uint4 s[VPT];
+#pragma unroll
+    for (int j = 0; j < VPT; ++j) {
+      const int c = threadIdx.x + j * blockDim.x;
+      if (c < p.hv) {
+        const size_t idx = row_vec0 + c;
+        if (TWOSHOT) {
+          s[j] = wait_one(my_hi + idx * 16, p, sg);
+        } else {
+          const uint4 own = ld_v4((const char*)p.in + idx * 16);
+          s[j] = gather_sum<T>(my_lo, nvec * 16, idx, own, p, sg);
+        }
+      }
+    }
+    row_epilogue<T, VPT>(s, row_vec0, p, smem);
+  }
+
+  finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
+                                : (unsigned long long)p.world * nvec * 16,
+              TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
+}
+
+// ---- plain all-reduce (no epilogue): flat vector indexing -----------------------------------------
+template <typename T, bool TWOSHOT>
+__device__ __forceinline__ void ar_body(const RankParams& p) {
+  const uint32_t epoch = p.st->epoch;
+  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  const size_t nvec = (size_t)p.nvec;
+  const size_t chunk = (nvec + p.world - 1) / p.world;
+  char* my_lo = lam_region(p, p.rank, b);
+  char* my_hi = my_lo + p.g.hi_off;
+  SpinGuard sg;
+
+  for (size_t idx = gtid; idx < nvec; idx += gsize) {
+    uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+    scrub(v);
+    if (!TWOSHOT) {
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < p.world && r != p.rank)
+          st_push_v4(lam_region(p, r, b) + ((size_t)p.rank * nvec + idx) * 16, v);
+    } else {
+      const int owner = (int)(idx / chunk);
+      if (owner != p.rank)
+        st_push_v4(lam_region(p, owner, b) + ((size_t)p.rank * chunk + (idx - owner * chunk)) * 16,
+                   v);
+    }
+  }
+  {
+    char* prev = lam_region(p, p.rank, pb);
+    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
+    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
+  }
+  if (TWOSHOT) {
+    const size_t lo = (size_t)p.rank * chunk;
+    const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+    for (size_t i = lo + gtid; i < hi; i += gsize) {
+      const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
+      uint4 s = gather_sum<T>(my_lo, chunk * 16, i - lo, own, p, sg);
+      scrub(s);
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
+    }
+    for (size_t idx = gtid; idx < nvec; idx += gsize)
+      st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
+  } else {
+    for (size_t idx = gtid; idx < nvec; idx += gsize) {
+      const uint4 own = ld_v4((const char*)p.in + idx * 16);
+      st_v4((char*)p.out + idx * 16, gather_sum<T>(my_lo, nvec * 16, idx, own, p, sg));
+    }
+  }
+  finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
+                                : (unsigned long long)p.world * nvec * 16,
+              TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
+}
+
+// ---- kernels: a real launch carries one rank, an emulated launch carries all of them ----------
+
+template <typename T, int VPT, bool TWOSHOT>
+__global__ void __launch_bounds__(512) ar_norm_kernel(const __grid_constant__ RankParams p) {
+  __shared__ float smem[34];
+  ar_norm_body<T, VPT, TWOSHOT>(p, smem);
+}
+
+template <typename T, int VPT, bool TWOSHOT>
+__global__ void __launch_bounds__(512) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
+  __shared__ float smem[34];
+  ar_norm_body<T, VPT, TWOSHOT>(ep.r[blockIdx.y], smem);
+}
+
+template <typename T, bool TWOSHOT>
+__global__ void __launch_bounds__(512) ar_kernel(const __grid_constant__ RankParams p) {
+  ar_body<T, TWOSHOT>(p);
+}
+
+template <typename T, bool TWOSHOT>
+__global__ void __launch_bounds__(512) ar_kernel_emu(const __grid_constant__ EmuParams ep) {
+  ar_body<T, TWOSHOT>(ep.r[blockIdx.y]);
+}
+
+// ---- local norm kernels (TP=1 and the unfused path) ---------------------------------------------
+// residual add + RMSNorm on rows of `in` (res_in == nullptr: plain rms_norm).
+template <typename T, int VPT>
+__global__ void __launch_bounds__(512) norm_kernel(const __grid_constant__ RankParams p) {
+  __shared__ float smem[34];
+  for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
+    const size_t row_vec0 = (size_t)row * p.hv;
+    uint4 s[VPT];
+#pragma unroll
+    for (int j = 0; j < VPT; ++j) {
+      const int c = threadIdx.x + j * blockDim.x;
+      if (c < p.hv) s[j] = ld_stream_v4((const char*)p.in + (row_vec0 + c) * 16);
+    }
+    row_epilogue<T, VPT>(s, row_vec0, p, smem);
+  }
+}
+
+// ---- all-gather along the last dim (byte-exact; flag protocol) -----------------------------------
+// Staging layout in every rank's arena = the final [rows][world][row_bytes] layout, double
+// buffered on the call parity.  Each rank pushes its slab into all peers' staging, fences,
+// and its last CTA raises flag[parity][rank] = seq+1 on every peer; receivers copy a
+// source's slab out as soon as that source's flag is up.
+struct CopyParams {
+  char* arena[kMaxRanks];
+  LocalState* st;
+  ArenaGeom g;
+  const void* in;
+  void* out;
+  int rank, world;
+  int rows;
+  int peer;  // send: dst, recv: src
+  unsigned long long row_vecs;  // 16-byte vectors per slab row
+  unsigned long long nvec;      // p2p: message vectors
+  unsigned long long timeout_ns;
+  int role;  // emu sendrecv: 0 = sender, 1 = receiver
+};
+
+struct EmuCopyParams {
+  CopyParams r[kMaxRanks];
+};
+
+__device__ __forceinline__ uint32_t* ctrl_flag(char* arena, size_t off, int i) {
+  return reinterpret_cast<uint32_t*>(arena + off + (size_t)i * kFlagStride);
+}
+
+__device__ __forceinline__ void wait_flag_ge(const uint32_t* f, uint32_t want, const CopyParams& p,
+                                             SpinGuard& sg) {
+  while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
+    if (sg.expired(p.timeout_ns, &p.st->error)) break;
+  }
+}
+
+__device__ __forceinline__ void all_gather_body(const CopyParams& p) {
+  const uint32_t seq = p.st->ag_seq;
+  const uint32_t par = seq & 1u;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  const size_t rv = (size_t)p.row_vecs;
+  const size_t slab_vecs = rv * (size_t)p.rows;
+  const size_t stage_off = p.g.ag_off + (size_t)par * p.g.ag_stride;
+  SpinGuard sg;
+
+  // push my slab: vector (row, c) -> staging[(row*world + rank)*rv + c] on every peer;
+  // my own slab goes straight to `out`.
+  for (size_t i = gtid; i < slab_vecs; i += gsize) {
+    const size_t row = i / rv, c = i - row * rv;
+    const uint4 v = ld_stream_v4((const char*)p.in + i * 16);
+    const size_t dst = ((row * p.world + p.rank) * rv + c) * 16;
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < p.world && r != p.rank) st_push_v4(p.arena[r] + stage_off + dst, v);
+    st_v4((char*)p.out + dst, v);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(&p.st->ag_arrive_push, 1u);
+    if (prev == gridDim.x - 1) {
+      p.st->ag_arrive_push = 0;
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r)
+        if (r != p.rank)
+          st_release_sys(ctrl_flag(p.arena[r], kAgFlagOff, (int)par * kMaxRanks + p.rank), seq + 1);
+    }
+  }
+  // copy the other ranks' slabs out of my staging as they complete
+  const char* stage = p.arena[p.rank] + stage_off;
+  for (int k = 1; k < p.world; ++k) {
+    const int src = (p.rank + k) % p.world;
+    wait_flag_ge(ctrl_flag(p.arena[p.rank], kAgFlagOff, (int)par * kMaxRanks + src), seq + 1, p, sg);
+    for (size_t i = gtid; i < slab_vecs; i += gsize) {
+      const size_t row = i / rv, c = i - row * rv;
+      const size_t off = ((row * p.world + src) * rv + c) * 16;
+      st_v4((char*)p.out + off, ld_poll_v4(stage + off));
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(&p.st->ag_arrive_done, 1u);
+    if (prev == gridDim.x - 1) {
+      p.st->ag_arrive_done = 0;
+      __threadfence();
+      p.st->ag_seq = seq + 1;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512) all_gather_kernel(const __grid_constant__ CopyParams p) {
+  all_gather_body(p);
+}
+__global__ void __launch_bounds__(512)
+    all_gather_kernel_emu(const __grid_constant__ EmuCopyParams ep) {
+  all_gather_body(ep.r[blockIdx.y]);
+}
+
+// ---- pipeline-stage send / recv (mailbox + ready flag + credit) ---------------------------------
+// Message m between a pair uses mailbox slot m&1 in the RECEIVER's arena.  The sender waits
+// for the credit of message m-2 (slot free), pushes, fences, and its last CTA raises
+// ready[src][slot] = m+1.  The receiver waits for ready, copies out, and its last CTA
+// returns credit[dst][slot] = m+1 into the SENDER's arena.
+__device__ __forceinline__ void send_body(const CopyParams& p) {
+  const uint32_t m = p.st->send_seq[p.peer];
+  const uint32_t slot = m & 1u;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  SpinGuard sg;
+  // credit[dst][slot] counts consumed messages of that slot: need >= m-1 (message m-2 done)
+  if (m >= 2)
+    wait_flag_ge(ctrl_flag(p.arena[p.rank], kP2pCreditOff, p.peer * 2 + (int)slot), m - 1, p, sg);
+  char* box = p.arena[p.peer] + p.g.p2p_off + ((size_t)p.rank * 2 + slot) * p.g.p2p_stride;
+  for (size_t i = gtid; i < (size_t)p.nvec; i += gsize)
+    st_push_v4(box + i * 16, ld_stream_v4((const char*)p.in + i * 16));
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(&p.st->p2p_arrive, 1u);
+    if (prev == gridDim.x - 1) {
+      p.st->p2p_arrive = 0;
+      __threadfence_system();
+      st_release_sys(ctrl_flag(p.arena[p.peer], kP2pReadyOff, p.rank * 2 + (int)slot), m + 1);
+      p.st->send_seq[p.peer] = m + 1;
+    }
+  }
+}
+
+__device__ __forceinline__ void recv_body(const CopyParams& p) {
+  const uint32_t m = p.st->recv_seq[p.peer];
+  const uint32_t slot = m & 1u;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  SpinGuard sg;
+  wait_flag_ge(ctrl_flag(p.arena[p.rank], kP2pReadyOff, p.peer * 2 + (int)slot), m + 1, p, sg);
+  const char* box = p.arena[p.rank] + p.g.p2p_off + ((size_t)p.peer * 2 + slot) * p.g.p2p_stride;
+  for (size_t i = gtid; i < (size_t)p.nvec; i += gsize)
+    st_v4((char*)p.out + i * 16, ld_poll_v4(box + i * 16));
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(&p.st->p2p_arrive, 1u);
+    if (prev == gridDim.x - 1) {
+      p.st->p2p_arrive = 0;
+      __threadfence_system();
+      st_release_sys(ctrl_flag(p.arena[p.peer], kP2pCreditOff, p.rank * 2 + (int)slot), m + 1);
+      p.st->recv_seq[p.peer] = m + 1;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512) send_kernel(const __grid_constant__ CopyParams p) {
+  send_body(p);
+}
+__global__ void __launch_bounds__(512) recv_kernel(const __grid_constant__ CopyParams p) {
+  recv_body(p);
+}
+__global__ void __launch_bounds__(512)
+    sendrecv_kernel_emu(const __grid_constant__ EmuCopyParams ep) {
+  const CopyParams& p = ep.r[blockIdx.y];
+  if (p.role == 0)
+    send_body(p);
+  else
+    recv_body(p);
+}
+
+// ---- arena initialisation ---------------------------------------------------------------------------
+__global__ void fill_not_arrived_kernel(uint4* p, size_t nvec) {
+  const uint4 m = make_uint4(kNotArrived, kNotArrived, kNotArrived, kNotArrived);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (size_t)gridDim.x * blockDim.x)
+    p[i] = m;
+}
+
+}  // namespace b200c
