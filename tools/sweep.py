@@ -1,0 +1,187 @@
+#!/usr/bin/env python3
+"""Per-size sweep of the fused all-reduce + residual + RMSNorm (BASELINE config 5) on real GPUs.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29511 tools/sweep.py --out gpurun_out/sweep_tpN.json
+
+For every (hidden, tokens) it times, as CUDA graphs of back-to-back calls (max over ranks):
+  ours one-shot / two-shot (several CTA counts), the unfused pair NCCL all-reduce + our norm
+  kernel, NCCL alone, and -- when it JIT-builds on the box -- FlashInfer's fused
+  trtllm_allreduce_fusion (the reference's Blackwell kernel).
+Prints a table on rank 0 and writes JSON; the measured crossover feeds the AUTO threshold.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from vllm_distributed_b200 import _cabi as C  # noqa: E402
+from vllm_distributed_b200 import comm as bc  # noqa: E402
+
+
+def time_graph(fn, iters, reps, dev, n):
+    """fn(i) enqueues call i; returns us per call (min over reps, max over ranks)."""
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        for i in range(3):
+            fn(i)
+    torch.cuda.synchronize()
+    dist.barrier()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            for i in range(iters):
+                fn(i)
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(reps):
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(s):
+            a.record(s)
+            g.replay()
+            b.record(s)
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        best = ms if best is None else min(best, ms)
+    t = torch.tensor([best], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    del g
+    return float(t.item()) * 1e3 / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="gpurun_out/sweep.json")
+    ap.add_argument("--hidden", type=int, nargs="+", default=[8192, 4096])
+    ap.add_argument("--max-tokens", type=int, default=8192)
+    ap.add_argument("--blocks", type=int, nargs="+", default=[32, 74, 148, 296])
+    ap.add_argument("--no-flashinfer", action="store_true")
+    ap.add_argument("--quick", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ["RANK"])
+    n = int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    cpu = dist.new_group(backend="gloo")
+    max_bytes = args.max_tokens * max(args.hidden) * 2
+    comm = bc.B200Comm.from_process_group(cpu, dev, max_bytes=max_bytes, ag_bytes=1 << 20,
+                                          p2p_bytes=1 << 20)
+    comm.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, 5000)
+
+    fi = None
+    if not args.no_flashinfer:
+        try:
+            import flashinfer.comm as ficomm
+            t0 = time.time()
+            ws = ficomm.create_allreduce_fusion_workspace(
+                backend="trtllm", world_size=n, rank=rank, max_token_num=args.max_tokens,
+                hidden_dim=max(args.hidden), dtype=torch.bfloat16, group=dist.group.WORLD)
+            fi = (ficomm, ws)
+            if rank == 0:
+                print(f"flashinfer workspace ready in {time.time() - t0:.1f}s", file=sys.stderr)
+        except Exception as e:  # noqa: BLE001
+            if rank == 0:
+                print(f"flashinfer comparator unavailable: {type(e).__name__}: {e}", file=sys.stderr)
+
+    rows = []
+    tokens = [1 << i for i in range(0, 14) if (1 << i) <= args.max_tokens]
+    if args.quick:
+        tokens = [t for t in tokens if t in (1, 16, 64, 256, 1024, 4096)]
+    NBUF = 4
+    for H in args.hidden:
+        gamma = torch.randn(H, device=dev).bfloat16()
+        for T in tokens:
+            S = T * H * 2
+            iters = 20 if S <= (4 << 20) else 6
+            xs = [torch.randn(T, H, device=dev).bfloat16() for _ in range(NBUF)]
+            res = torch.randn(T, H, device=dev).bfloat16()
+            out = torch.empty_like(res)
+            row = {"hidden": H, "tokens": T, "bytes": S, "n": n}
+
+            def ours(variant):
+                return lambda i: comm.all_reduce_add_rmsnorm_into(xs[i % NBUF], res, gamma, 1e-5,
+                                                                 out, variant)
+            if S * n <= 2 * max_bytes and S <= (8 << 20):
+                best = None
+                for blk in args.blocks:
+                    comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, blk)
+                    us = time_graph(ours(C.ONESHOT), iters, 3, dev, n)
+                    row[f"oneshot_b{blk}_us"] = round(us, 2)
+                    best = us if best is None else min(best, us)
+                row["oneshot_us"] = round(best, 2)
+            best = None
+            for blk in args.blocks:
+                comm.set_tuning(C.TUNE_TWOSHOT_BLOCKS, blk)
+                us = time_graph(ours(C.TWOSHOT), iters, 3, dev, n)
+                row[f"twoshot_b{blk}_us"] = round(us, 2)
+                best = us if best is None else min(best, us)
+            row["twoshot_us"] = round(best, 2)
+            # plain all-reduce (no epilogue), both variants at default CTA counts
+            comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 148)
+            comm.set_tuning(C.TUNE_TWOSHOT_BLOCKS, 148)
+            if S * n <= 2 * max_bytes and S <= (8 << 20):
+                row["ar_oneshot_us"] = round(time_graph(
+                    lambda i: comm.all_reduce(xs[i % NBUF], C.ONESHOT, out), iters, 3, dev, n), 2)
+            row["ar_twoshot_us"] = round(time_graph(
+                lambda i: comm.all_reduce(xs[i % NBUF], C.TWOSHOT, out), iters, 3, dev, n), 2)
+
+            # NCCL all-reduce alone, and the unfused pair (NCCL + our local norm kernel)
+            tmp = [torch.empty_like(x) for x in xs]
+
+            def nccl_only(i):
+                tmp[i % NBUF].copy_(xs[i % NBUF])
+                dist.all_reduce(tmp[i % NBUF])
+
+            def nccl_pair(i):
+                nccl_only(i)
+                bc.fused_add_rms_norm_(tmp[i % NBUF], res, gamma, 1e-5)
+            row["nccl_ar_us"] = round(time_graph(nccl_only, iters, 3, dev, n), 2)
+            row["nccl_pair_us"] = round(time_graph(nccl_pair, iters, 3, dev, n), 2)
+
+            if fi is not None and T > n:  # two-shot asserts token_num > world_size
+                ficomm, ws = fi
+                try:
+                    ro, no = torch.empty_like(res), torch.empty_like(res)
+
+                    def fi_call(i, oneshot=None):
+                        ficomm.allreduce_fusion(
+                            input=xs[i % NBUF], workspace=ws,
+                            pattern=ficomm.AllReduceFusionPattern.kARResidualRMSNorm,
+                            launch_with_pdl=True, trigger_completion_at_end=T > 16,
+                            residual_out=ro, norm_out=no, residual_in=res, rms_gamma=gamma,
+                            rms_eps=1e-5, use_oneshot=oneshot, fp32_acc=True)
+                    row["flashinfer_auto_us"] = round(time_graph(fi_call, iters, 3, dev, n), 2)
+                except Exception as e:  # noqa: BLE001
+                    row["flashinfer_error"] = f"{type(e).__name__}: {e}"[:200]
+            bus = 2 * (n - 1) / n * S
+            best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us"))
+            row["best_us"] = best
+            row["bus_gbs"] = round(bus / best / 1e3, 1)
+            rows.append(row)
+            if rank == 0:
+                print(json.dumps(row), file=sys.stderr, flush=True)
+            comm.check_health()
+    if rank == 0:
+        os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+        json.dump({"n": n, "rows": rows}, open(args.out, "w"), indent=1)
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -177,6 +177,15 @@ class B200Comm:
             gamma.data_ptr(), float(eps), tokens, hidden, DTYPE_CODE[x.dtype], variant, _stream()))
         return norm_out, res_out
 
+    def all_reduce_add_rmsnorm_into(self, x: torch.Tensor, residual: torch.Tensor,
+                                    gamma: torch.Tensor, eps: float, norm_out: torch.Tensor,
+                                    variant: int = C.AUTO) -> None:
+        """residual updated in place (the residual stream), normalised output into norm_out."""
+        tokens, hidden = _rows(x)
+        C.check(C.lib().b200c_all_reduce_add_rmsnorm(
+            self.ctx, x.data_ptr(), residual.data_ptr(), residual.data_ptr(), norm_out.data_ptr(),
+            gamma.data_ptr(), float(eps), tokens, hidden, DTYPE_CODE[x.dtype], variant, _stream()))
+
     def all_gather_lastdim(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
         rows, cols = _rows(x)
         if out is None:

@@ -100,11 +100,22 @@ void fill_copy_params(const b200c_ctx* c, CopyParams& p) {
 }
 
 // Every CTA of a collective kernel must be resident at once (CTAs wait on peers' CTAs).
+// The occupancy answer is cached per (kernel, block size): it is asked on every launch.
 template <typename K>
 int coresident_blocks(K kernel, int threads, int sm_count, int* out) {
+  static thread_local struct { const void* fn; int threads; int per_sm; } cache[8] = {};
+  const void* key = reinterpret_cast<const void*>(kernel);
+  for (auto& e : cache)
+    if (e.fn == key && e.threads == threads) {
+      *out = e.per_sm * sm_count;
+      return B200C_OK;
+    }
   int per_sm = 0;
   CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
   if (per_sm < 1) return fail(B200C_ECUDA, "kernel cannot be resident with %d threads", threads);
+  static thread_local int next = 0;
+  cache[next] = {key, threads, per_sm};
+  next = (next + 1) % 8;
   *out = per_sm * sm_count;
   return B200C_OK;
 }
@@ -352,10 +363,12 @@ int check_emu(b200c_ctx* const* ctxs, int world) {
   return B200C_OK;
 }
 
-int copy_grid(const b200c_ctx* c, size_t nvec, int nemu, void* kernel_fn, int* g) {
-  int per_sm = 0;
-  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel_fn, 512, 0));
-  int cap = std::max(1, per_sm * c->sm_count / std::max(1, nemu));
+template <typename K>
+int copy_grid(const b200c_ctx* c, size_t nvec, int nemu, K kernel_fn, int* g) {
+  int cap = 0;
+  int rc = coresident_blocks(kernel_fn, 512, c->sm_count, &cap);
+  if (rc) return rc;
+  cap = std::max(1, cap / std::max(1, nemu));
   size_t want = std::min<size_t>((size_t)c->copy_blocks, (nvec + 511) / 512);
   *g = (int)std::max<size_t>(1, std::min<size_t>(want, (size_t)cap));
   return B200C_OK;
@@ -604,11 +617,11 @@ static int all_gather_impl(b200c_ctx* const* ctxs, int nemu, const void* const* 
   }
   int g = 1;
   if (nemu == 0) {
-    int rc = copy_grid(c0, slab_vecs, 0, (void*)all_gather_kernel, &g);
+    int rc = copy_grid(c0, slab_vecs, 0, all_gather_kernel, &g);
     if (rc) return rc;
     return launch(all_gather_kernel, dim3(g, 1, 1), 512, cp[0], s, false);
   }
-  int rc = copy_grid(c0, slab_vecs, nemu, (void*)all_gather_kernel_emu, &g);
+  int rc = copy_grid(c0, slab_vecs, nemu, all_gather_kernel_emu, &g);
   if (rc) return rc;
   EmuCopyParams ep;
   memset(&ep, 0, sizeof(ep));
@@ -645,7 +658,7 @@ int b200c_send(b200c_ctx* c, int dst, const void* buf, size_t bytes, void* strea
   cp.peer = dst;
   cp.nvec = bytes / 16;
   int g = 1;
-  rc = copy_grid(c, cp.nvec, 0, (void*)send_kernel, &g);
+  rc = copy_grid(c, cp.nvec, 0, send_kernel, &g);
   if (rc) return rc;
   return launch(send_kernel, dim3(g, 1, 1), 512, cp, static_cast<cudaStream_t>(stream), false);
 }
@@ -660,7 +673,7 @@ int b200c_recv(b200c_ctx* c, int src, void* buf, size_t bytes, void* stream) {
   cp.peer = src;
   cp.nvec = bytes / 16;
   int g = 1;
-  rc = copy_grid(c, cp.nvec, 0, (void*)recv_kernel, &g);
+  rc = copy_grid(c, cp.nvec, 0, recv_kernel, &g);
   if (rc) return rc;
   return launch(recv_kernel, dim3(g, 1, 1), 512, cp, static_cast<cudaStream_t>(stream), false);
 }
@@ -719,7 +732,7 @@ int b200c_emu_sendrecv(b200c_ctx* const* ctxs, int world, int src, int dst, cons
   ep.r[1].nvec = bytes / 16;
   ep.r[1].role = 1;
   int g = 1;
-  rc = copy_grid(ctxs[src], bytes / 16, 2, (void*)sendrecv_kernel_emu, &g);
+  rc = copy_grid(ctxs[src], bytes / 16, 2, sendrecv_kernel_emu, &g);
   if (rc) return rc;
   return launch(sendrecv_kernel_emu, dim3(g, 2, 1), 512, ep, static_cast<cudaStream_t>(stream), true);
 }
