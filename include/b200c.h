@@ -52,7 +52,8 @@ extern "C" {
 #define B200C_TUNE_TWOSHOT_BLOCKS 3    /* CTAs for the two-shot kernels             */
 #define B200C_TUNE_SPIN_TIMEOUT_MS 4   /* device-side wait timeout, 0 = wait forever */
 #define B200C_TUNE_COPY_BLOCKS 5       /* CTAs for all-gather / send / recv          */
-#define B200C_TUNE_NORM_ROWS_PER_CTA 6 /* reserved */
+#define B200C_TUNE_LINK_BLOCKS 6       /* two-shot CTAs doing link work; 0 = half the grid */
+#define B200C_TUNE_PDL 7               /* programmatic dependent launch on/off (default on) */
 
 typedef struct b200c_ctx b200c_ctx;
 

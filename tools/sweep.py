@@ -65,7 +65,8 @@ def main():
     ap.add_argument("--out", default="gpurun_out/sweep.json")
     ap.add_argument("--hidden", type=int, nargs="+", default=[8192, 4096])
     ap.add_argument("--max-tokens", type=int, default=8192)
-    ap.add_argument("--blocks", type=int, nargs="+", default=[32, 74, 148, 296])
+    ap.add_argument("--blocks", type=int, nargs="+", default=[148, 296])
+    ap.add_argument("--link", type=int, nargs="+", default=[24, 48, 74, 110])
     ap.add_argument("--no-flashinfer", action="store_true")
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
@@ -116,19 +117,23 @@ def main():
                 return lambda i: comm.all_reduce_add_rmsnorm_into(xs[i % NBUF], res, gamma, 1e-5,
                                                                  out, variant)
             if S * n <= 2 * max_bytes and S <= (8 << 20):
-                best = None
-                for blk in args.blocks:
-                    comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, blk)
-                    us = time_graph(ours(C.ONESHOT), iters, 3, dev, n)
-                    row[f"oneshot_b{blk}_us"] = round(us, 2)
-                    best = us if best is None else min(best, us)
-                row["oneshot_us"] = round(best, 2)
+                comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 148)
+                for pdl in (1, 0):
+                    comm.set_tuning(C.TUNE_PDL, pdl)
+                    row[f"oneshot_pdl{pdl}_us"] = round(time_graph(ours(C.ONESHOT), iters, 3, dev, n), 2)
+                comm.set_tuning(C.TUNE_PDL, 1)
+                row["oneshot_us"] = min(row["oneshot_pdl1_us"], row["oneshot_pdl0_us"])
             best = None
             for blk in args.blocks:
-                comm.set_tuning(C.TUNE_TWOSHOT_BLOCKS, blk)
-                us = time_graph(ours(C.TWOSHOT), iters, 3, dev, n)
-                row[f"twoshot_b{blk}_us"] = round(us, 2)
-                best = us if best is None else min(best, us)
+                for link in args.link:
+                    if link >= blk:
+                        continue
+                    comm.set_tuning(C.TUNE_TWOSHOT_BLOCKS, blk)
+                    comm.set_tuning(C.TUNE_LINK_BLOCKS, link)
+                    us = time_graph(ours(C.TWOSHOT), iters, 3, dev, n)
+                    row[f"twoshot_b{blk}_l{link}_us"] = round(us, 2)
+                    best = us if best is None else min(best, us)
+            comm.set_tuning(C.TUNE_LINK_BLOCKS, 0)
             row["twoshot_us"] = round(best, 2)
             # plain all-reduce (no epilogue), both variants at default CTA counts
             comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 148)

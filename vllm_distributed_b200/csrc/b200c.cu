@@ -64,6 +64,8 @@ struct b200c_ctx {
   int twoshot_blocks = 148;
   int copy_blocks = 64;
   long long spin_timeout_ms = 10000;
+  int link_blocks = 0;  // two-shot CTAs doing link work; 0 = half of the grid
+  int pdl = 1;          // programmatic dependent launch on the real (non-emulated) kernels
 };
 
 namespace {
@@ -121,7 +123,8 @@ int coresident_blocks(K kernel, int threads, int sm_count, int* out) {
 }
 
 template <typename K, typename P>
-int launch(K kernel, dim3 grid, int threads, const P& params, cudaStream_t s, bool cooperative) {
+int launch(K kernel, dim3 grid, int threads, const P& params, cudaStream_t s, bool cooperative,
+           bool pdl = false) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid;
@@ -134,9 +137,23 @@ int launch(K kernel, dim3 grid, int threads, const P& params, cudaStream_t s, bo
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+  } else if (pdl) {
+    // the kernel may start while its predecessor drains; it blocks in griddepcontrol.wait
+    // before touching anything the predecessor produces
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
   }
   CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, params));
   return B200C_OK;
+}
+
+// two-shot role split: CTAs [0, link) push over the link, the rest run the rows
+int link_split(const b200c_ctx* c, int grid) {
+  if (grid < 2) return 0;
+  int l = c->link_blocks > 0 ? c->link_blocks : grid / 2;
+  return std::max(1, std::min(l, grid - 1));
 }
 
 // rows are split over `threads` lanes holding up to VPT vectors each
@@ -179,7 +196,10 @@ int launch_ar_norm_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int
     int rc = coresident_blocks(ar_norm_kernel<T, VPT, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
     if (rc) return rc;
     const int g = std::max(1, std::min(want_blocks, cap));
-    return launch(ar_norm_kernel<T, VPT, TWOSHOT>, dim3(g, 1, 1), threads, rp[0], s, false);
+    RankParams p = rp[0];
+    p.link_blocks = TWOSHOT ? link_split(ctxs[0], g) : 0;
+    return launch(ar_norm_kernel<T, VPT, TWOSHOT>, dim3(g, 1, 1), threads, p, s, false,
+                  ctxs[0]->pdl != 0);
   }
   int cap = 0;
   int rc = coresident_blocks(ar_norm_kernel_emu<T, VPT, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
@@ -187,7 +207,10 @@ int launch_ar_norm_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int
   const int g = std::max(1, std::min(want_blocks, cap / nemu));
   EmuParams ep;
   memset(&ep, 0, sizeof(ep));
-  for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
+  for (int r = 0; r < nemu; ++r) {
+    ep.r[r] = rp[r];
+    ep.r[r].link_blocks = TWOSHOT ? link_split(ctxs[0], g) : 0;
+  }
   return launch(ar_norm_kernel_emu<T, VPT, TWOSHOT>, dim3(g, nemu, 1), threads, ep, s, true);
 }
 
@@ -216,7 +239,9 @@ int launch_ar_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int want
     int rc = coresident_blocks(ar_kernel<T, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
     if (rc) return rc;
     const int g = std::max(1, std::min(want_blocks, cap));
-    return launch(ar_kernel<T, TWOSHOT>, dim3(g, 1, 1), threads, rp[0], s, false);
+    RankParams p = rp[0];
+    p.link_blocks = TWOSHOT ? link_split(ctxs[0], g) : 0;
+    return launch(ar_kernel<T, TWOSHOT>, dim3(g, 1, 1), threads, p, s, false, ctxs[0]->pdl != 0);
   }
   int cap = 0;
   int rc = coresident_blocks(ar_kernel_emu<T, TWOSHOT>, threads, ctxs[0]->sm_count, &cap);
@@ -224,28 +249,32 @@ int launch_ar_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int want
   const int g = std::max(1, std::min(want_blocks, cap / nemu));
   EmuParams ep;
   memset(&ep, 0, sizeof(ep));
-  for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
+  for (int r = 0; r < nemu; ++r) {
+    ep.r[r] = rp[r];
+    ep.r[r].link_blocks = TWOSHOT ? link_split(ctxs[0], g) : 0;
+  }
   return launch(ar_kernel_emu<T, TWOSHOT>, dim3(g, nemu, 1), threads, ep, s, true);
 }
 
 template <typename T>
-int launch_norm_only(const RankParams& rp, int vpt, int threads, int sm_count, cudaStream_t s) {
+int launch_norm_only(const RankParams& rp, int vpt, int threads, int sm_count, cudaStream_t s,
+                     bool pdl) {
   const int g = std::max(1, std::min(rp.tokens, sm_count * 16));
   switch (vpt) {
-    case 1: return launch(norm_kernel<T, 1>, dim3(g, 1, 1), threads, rp, s, false);
-    case 2: return launch(norm_kernel<T, 2>, dim3(g, 1, 1), threads, rp, s, false);
-    case 4: return launch(norm_kernel<T, 4>, dim3(g, 1, 1), threads, rp, s, false);
+    case 1: return launch(norm_kernel<T, 1>, dim3(g, 1, 1), threads, rp, s, false, pdl);
+    case 2: return launch(norm_kernel<T, 2>, dim3(g, 1, 1), threads, rp, s, false, pdl);
+    case 4: return launch(norm_kernel<T, 4>, dim3(g, 1, 1), threads, rp, s, false, pdl);
   }
   return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
 }
 
-int norm_only(RankParams& rp, int dtype, int sm_count, cudaStream_t s) {
+int norm_only(RankParams& rp, int dtype, int sm_count, cudaStream_t s, bool pdl = true) {
   int vpt, threads;
   norm_shape(rp.hv, &vpt, &threads);
   switch (dtype) {
-    case B200C_BF16: return launch_norm_only<__nv_bfloat16>(rp, vpt, threads, sm_count, s);
-    case B200C_F16: return launch_norm_only<__half>(rp, vpt, threads, sm_count, s);
-    case B200C_F32: return launch_norm_only<float>(rp, vpt, threads, sm_count, s);
+    case B200C_BF16: return launch_norm_only<__nv_bfloat16>(rp, vpt, threads, sm_count, s, pdl);
+    case B200C_F16: return launch_norm_only<__half>(rp, vpt, threads, sm_count, s, pdl);
+    case B200C_F32: return launch_norm_only<float>(rp, vpt, threads, sm_count, s, pdl);
   }
   return fail(B200C_EINVAL, "bad dtype %d", dtype);
 }
@@ -296,7 +325,7 @@ int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
     rp[r].hidden = hidden;
     rp[r].nvec = (unsigned long long)tokens * hv;
   }
-  if (c0->world == 1) return norm_only(rp[0], dtype, c0->sm_count, s);
+  if (c0->world == 1) return norm_only(rp[0], dtype, c0->sm_count, s, c0->pdl != 0);
 
   const size_t bytes = (size_t)tokens * hv * 16;
   variant = pick_variant(c0, bytes, variant);
@@ -344,6 +373,7 @@ int ar_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins, void* cons
   const size_t nvec = bytes / 16;
   int want = two ? c0->twoshot_blocks : c0->oneshot_blocks;
   want = (int)std::min<size_t>((size_t)want, (nvec + 511) / 512);
+  if (two) want = std::max(want, 2);
 #define B200C_AR(T) \
   (two ? launch_ar_t<T, true>(ctxs, nemu, rp, want, s) : launch_ar_t<T, false>(ctxs, nemu, rp, want, s))
   switch (dtype) {
@@ -498,6 +528,8 @@ int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
     case B200C_TUNE_TWOSHOT_BLOCKS: c->twoshot_blocks = (int)std::max<long long>(1, v); break;
     case B200C_TUNE_SPIN_TIMEOUT_MS: c->spin_timeout_ms = std::max<long long>(0, v); break;
     case B200C_TUNE_COPY_BLOCKS: c->copy_blocks = (int)std::max<long long>(1, v); break;
+    case B200C_TUNE_LINK_BLOCKS: c->link_blocks = (int)std::max<long long>(0, v); break;
+    case B200C_TUNE_PDL: c->pdl = v != 0; break;
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;
@@ -511,6 +543,8 @@ int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
     case B200C_TUNE_TWOSHOT_BLOCKS: *v = c->twoshot_blocks; break;
     case B200C_TUNE_SPIN_TIMEOUT_MS: *v = c->spin_timeout_ms; break;
     case B200C_TUNE_COPY_BLOCKS: *v = c->copy_blocks; break;
+    case B200C_TUNE_LINK_BLOCKS: *v = c->link_blocks; break;
+    case B200C_TUNE_PDL: *v = c->pdl; break;
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;

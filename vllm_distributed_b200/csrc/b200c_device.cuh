@@ -194,24 +194,29 @@ struct VecOps<float> {
 };
 
 // ---- block-wide sum (warp shuffles, one shared-memory hop) -------------------------------------
-// Fixed reduction tree => the same row gives the same bits on every rank.
-__device__ __forceinline__ float block_sum(float v, float* smem /* >= 33 floats */) {
+// Fixed reduction tree => the same row gives the same bits on every rank.  `smem` holds two
+// banks of 32 floats used alternately (parity flips per call), so one call costs ONE barrier:
+// a bank is rewritten two calls later, and reaching that call means every warp has passed the
+// barrier of the call in between, i.e. has finished reading the bank.
+__device__ __forceinline__ float block_sum(float v, float* smem /* 64 floats */, int& parity) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nwarps = (blockDim.x + 31) >> 5;
-  if (lane == 0) smem[warp] = v;
+  float* bank = smem + parity * 32;
+  parity ^= 1;
+  if (lane == 0) bank[warp] = v;
   __syncthreads();
-  if (warp == 0) {
-    float t = (lane < nwarps) ? smem[lane] : 0.0f;
+  float t = (lane < nwarps) ? bank[lane] : 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if (lane == 0) smem[32] = t;
-  }
-  __syncthreads();
-  float total = smem[32];
-  __syncthreads();  // smem is reused by the next row
-  return total;
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  return t;  // every warp reduces the same 32 partials in the same order
 }
+
+// ---- programmatic dependent launch (no-ops when the launch did not ask for it) -----------------
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 }  // namespace b200c

@@ -56,6 +56,7 @@ struct RankParams {
   int hidden;              // elements per row
   unsigned long long nvec;  // total 16-byte vectors
   unsigned long long timeout_ns;
+  int link_blocks;  // two-shot: CTAs [0, link_blocks) do the link work, the rest the rows
 };
 
 struct EmuParams {
@@ -78,42 +79,50 @@ __device__ __forceinline__ uint4 wait_one(const char* addr, const RankParams& p,
   return v;
 }
 
-// One-shot gather-and-sum of vector `idx`: slot r of my region holds rank r's copy; my own
-// contribution comes straight from `in`.  All world-1 polls are issued back to back so the
-// L2 round trips overlap; accumulation is fp32 in rank order 0..N-1 with one rounding (the
-// reference's packed_reduce order, vllm_custom_all_reduce.cuh:213-221).
-template <typename T>
+// Gather-and-sum of vector `idx`: slot r of my region holds rank r's copy; my own contribution
+// comes straight from `in`.  Polls are issued BATCH peers at a time so their L2 round trips
+// overlap (BATCH = 8: all at once, for the latency-bound one-shot; 4 keeps registers down in
+// the bandwidth-bound two-shot); accumulation is fp32 in rank order 0..N-1 with one rounding
+// (the reference's packed_reduce order, vllm_custom_all_reduce.cuh:213-221).
+template <typename T, int BATCH>
 __device__ __forceinline__ uint4 gather_sum(const char* my_lo, size_t slot_bytes, size_t idx,
                                             const uint4& own, const RankParams& p,
                                             SpinGuard& sg) {
   constexpr int EPV = VecOps<T>::EPV;
-  uint4 v[kMaxRanks];
-  const char* base = my_lo + idx * 16;
-  bool pending;
-  do {
-    pending = false;
-#pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < p.world && r != p.rank) v[r] = ld_poll_v4(base + (size_t)r * slot_bytes);
-    }
-#pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < p.world && r != p.rank) pending |= not_arrived(v[r]);
-    }
-    if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
-  } while (pending);
-
   float acc[EPV], f[EPV];
+  const char* base = my_lo + idx * 16;
 #pragma unroll
-  for (int r = 0; r < kMaxRanks; ++r) {
-    if (r < p.world) {
-      const uint4 x = (r == p.rank) ? own : v[r];
-      if (r == 0) {
-        VecOps<T>::to_float(x, acc);
-      } else {
-        VecOps<T>::to_float(x, f);
+  for (int r0 = 0; r0 < kMaxRanks; r0 += BATCH) {
+    if (r0 < p.world) {
+      uint4 v[BATCH];
+      bool pending;
+      do {
+        pending = false;
 #pragma unroll
-        for (int e = 0; e < EPV; ++e) acc[e] += f[e];
+        for (int k = 0; k < BATCH; ++k) {
+          const int r = r0 + k;
+          if (r < p.world && r != p.rank) v[k] = ld_poll_v4(base + (size_t)r * slot_bytes);
+        }
+#pragma unroll
+        for (int k = 0; k < BATCH; ++k) {
+          const int r = r0 + k;
+          if (r < p.world && r != p.rank) pending |= not_arrived(v[k]);
+        }
+        if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
+      } while (pending);
+#pragma unroll
+      for (int k = 0; k < BATCH; ++k) {
+        const int r = r0 + k;
+        if (r < p.world) {
+          const uint4 x = (r == p.rank) ? own : v[k];
+          if (r == 0) {
+            VecOps<T>::to_float(x, acc);
+          } else {
+            VecOps<T>::to_float(x, f);
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) acc[e] += f[e];
+          }
+        }
       }
     }
   }
@@ -147,12 +156,38 @@ __device__ __forceinline__ void finish_call(const RankParams& p, uint32_t epoch,
   }
 }
 
+// ---- pushes ----------------------------------------------------------------------------------------
+// Copy vectors [lo, hi) of `in` to dst + (i - lo)*16, `U` independent loads in flight per
+// thread (the loop is latency-bound otherwise: one 16-byte load per ~1 us per thread).
+template <int U>
+__device__ __forceinline__ void push_range(const char* in, char* dst, size_t lo, size_t hi,
+                                           size_t tid, size_t nthreads) {
+  for (size_t base = lo + tid; base < hi; base += nthreads * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * nthreads;
+      if (i < hi) v[u] = ld_stream_v4(in + i * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * nthreads;
+      if (i < hi) {
+        scrub(v[u]);
+        st_push_v4(dst + (i - lo) * 16, v[u]);
+      }
+    }
+  }
+}
+
 // ---- row epilogue: residual add + RMSNorm ------------------------------------------------------
-// x[j] holds the T-rounded all-reduce sum for vector (tid + j*blockDim) of the row.
+// s[j] holds the T-rounded all-reduce sum for vector (tid + j*blockDim) of the row, res[j] the
+// residual vector (prefetched before the wait), gam[j] the weight vector (loaded once per CTA).
 // VLLM/ir/ops/layernorm.py:39-58.
 template <typename T, int VPT>
-__device__ __forceinline__ void row_epilogue(uint4 (&s)[VPT], size_t row_vec0, const RankParams& p,
-                                             float* smem) {
+__device__ __forceinline__ void row_epilogue(const uint4 (&s)[VPT], const uint4 (&res)[VPT],
+                                             const uint4 (&gam)[VPT], size_t row_vec0,
+                                             const RankParams& p, float* smem, int& parity) {
   constexpr int EPV = VecOps<T>::EPV;
   float x[VPT][EPV];
   float ss = 0.0f;
@@ -163,8 +198,7 @@ __device__ __forceinline__ void row_epilogue(uint4 (&s)[VPT], size_t row_vec0, c
       VecOps<T>::to_float(s[j], x[j]);
       if (p.res_in != nullptr) {
         float r[EPV];
-        const uint4 rv = ld_stream_v4((const char*)p.res_in + (row_vec0 + c) * 16);
-        VecOps<T>::to_float(rv, r);
+        VecOps<T>::to_float(res[j], r);
 #pragma unroll
         for (int e = 0; e < EPV; ++e) x[j][e] = x[j][e] + r[e];
         st_v4((char*)p.res_out + (row_vec0 + c) * 16, VecOps<T>::from_float(x[j]));
@@ -173,14 +207,14 @@ __device__ __forceinline__ void row_epilogue(uint4 (&s)[VPT], size_t row_vec0, c
       for (int e = 0; e < EPV; ++e) ss += x[j][e] * x[j][e];
     }
   }
-  const float total = block_sum(ss, smem);
+  const float total = block_sum(ss, smem, parity);
   const float rs = 1.0f / sqrtf(total / (float)p.hidden + p.eps);
 #pragma unroll
   for (int j = 0; j < VPT; ++j) {
     const int c = threadIdx.x + j * blockDim.x;
     if (c < p.hv) {
       float g[EPV], y[EPV];
-      VecOps<T>::to_float(ld_v4((const char*)p.gamma + (size_t)c * 16), g);
+      VecOps<T>::to_float(gam[j], g);
 #pragma unroll
       for (int e = 0; e < EPV; ++e) y[e] = VecOps<T>::round_trip(x[j][e] * rs) * g[e];
       st_v4((char*)p.norm_out + (row_vec0 + c) * 16, VecOps<T>::from_float(y));
@@ -188,31 +222,67 @@ __device__ __forceinline__ void row_epilogue(uint4 (&s)[VPT], size_t row_vec0, c
   }
 }
 
+template <typename T, int VPT>
+__device__ __forceinline__ void load_gamma(uint4 (&gam)[VPT], const RankParams& p) {
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int c = threadIdx.x + j * blockDim.x;
+    if (c < p.hv) gam[j] = ld_v4((const char*)p.gamma + (size_t)c * 16);
+  }
+}
+
+template <int VPT>
+__device__ __forceinline__ void load_residual(uint4 (&res)[VPT], size_t row_vec0,
+                                              const RankParams& p) {
+  if (p.res_in == nullptr) return;
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int c = threadIdx.x + j * blockDim.x;
+    if (c < p.hv) res[j] = ld_stream_v4((const char*)p.res_in + (row_vec0 + c) * 16);
+  }
+}
+
 // ---- fused all-reduce + residual + RMSNorm ---------------------------------------------------
 //
-// ONE-SHOT (latency regime): phase A pushes my rows into slot[rank] of every peer's region,
-// phase C polls slot[r] for all r, sums, and runs the epilogue.  One fabric traversal, no
+// ONE-SHOT (latency regime): every CTA pushes its rows into slot[rank] of every peer's region,
+// then polls slot[r] for all r, sums, and runs the epilogue.  One fabric traversal, no
 // barrier.  Link traffic (N-1)*S out per rank.
 //
-// TWO-SHOT (bandwidth regime): phase A pushes vector chunk j of my input to rank j (scatter),
-// phase B reduces my chunk and pushes the T-rounded sums into the hi half of EVERY rank's
-// region (gather), phase C polls the gathered sums row by row and runs the epilogue on all
-// rows (local HBM work, an order of magnitude cheaper than the link).  Link traffic
+// TWO-SHOT (bandwidth regime): CTAs are specialised.  LINK CTAs [0, link_blocks) push vector
+// chunk j of the input to rank j (scatter), then reduce this rank's chunk and push the
+// T-rounded sums into the hi half of EVERY rank's region (gather).  ROW CTAs re-arm the
+// previous region, then poll the gathered sums row by row and run the epilogue on all rows
+// (local HBM work that overlaps the link work instead of following it).  Link traffic
 // 2*(N-1)/N*S out per rank.  CTAs wait only on data whose producers never wait on them, and
 // the grid is sized to be co-resident, so the kernel cannot deadlock.
 template <typename T, int VPT, bool TWOSHOT>
 __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
+  pdl_launch_dependents();
+  uint4 gam[VPT];
+  load_gamma<T, VPT>(gam, p);  // weights: safe to read before the previous kernel has finished
+  pdl_wait();
+
   const uint32_t epoch = p.st->epoch;
   const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
-  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const size_t gsize = (size_t)gridDim.x * blockDim.x;
   const size_t nvec = (size_t)p.nvec;
   const size_t chunk = (nvec + p.world - 1) / p.world;  // two-shot: vectors owned per rank
   char* my_lo = lam_region(p, p.rank, b);
   char* my_hi = my_lo + p.g.hi_off;
   SpinGuard sg;
+  int parity = 0;
 
-  // ---- phase A: push
+  const int link_blocks = TWOSHOT ? p.link_blocks : 0;
+  const bool specialised = TWOSHOT && link_blocks > 0 && link_blocks < (int)gridDim.x;
+  const bool is_link = !specialised || (int)blockIdx.x < link_blocks;
+  const bool is_row = !specialised || (int)blockIdx.x >= link_blocks;
+  const int row0 = specialised ? (int)blockIdx.x - link_blocks : (int)blockIdx.x;
+  const int row_stride = specialised ? (int)gridDim.x - link_blocks : (int)gridDim.x;
+  const size_t ltid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // valid for link CTAs
+  const size_t lsize = (size_t)(specialised ? link_blocks : gridDim.x) * blockDim.x;
+  const size_t rtid = (size_t)row0 * blockDim.x + threadIdx.x;
+  const size_t rsize = (size_t)row_stride * blockDim.x;
+
+  // ---- push
   if (!TWOSHOT) {
     const size_t slot_off = (size_t)p.rank * nvec * 16;
     for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
@@ -229,32 +299,33 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
         }
       }
     }
-  } else {
-    for (size_t idx = gtid; idx < nvec; idx += gsize) {
-      const int owner = (int)(idx / chunk);
-      if (owner != p.rank) {
-        uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
-        scrub(v);
-        st_push_v4(lam_region(p, owner, b) + ((size_t)p.rank * chunk + (idx - owner * chunk)) * 16,
-                   v);
-      }
+  } else if (is_link) {
+    // scatter: peer after peer, each rank starting at its right-hand neighbour so that at any
+    // moment the N ranks write to N different destinations
+    for (int k = 1; k < p.world; ++k) {
+      const int owner = (p.rank + k) % p.world;
+      const size_t lo = (size_t)owner * chunk;
+      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+      if (lo < hi)
+        push_range<4>((const char*)p.in, lam_region(p, owner, b) + (size_t)p.rank * chunk * 16, lo,
+                      hi, ltid, lsize);
     }
   }
 
   // ---- re-arm the previous call's region while the pushes are in flight
-  {
+  if (is_row) {
     char* prev = lam_region(p, p.rank, pb);
-    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
-    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
+    rearm(prev, p.st->dirty_lo[pb], rtid, rsize);
+    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], rtid, rsize);
   }
 
-  // ---- phase B (two-shot): reduce my chunk, push the sums to every rank's hi half
-  if (TWOSHOT) {
+  // ---- two-shot: reduce my chunk, push the sums to every rank's hi half
+  if (TWOSHOT && is_link) {
     const size_t lo = (size_t)p.rank * chunk;
     const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-    for (size_t i = lo + gtid; i < hi; i += gsize) {
+    for (size_t i = lo + ltid; i < hi; i += lsize) {
       const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
-      uint4 s = gather_sum<T>(my_lo, chunk * 16, i - lo, own, p, sg);
+      uint4 s = gather_sum<T, 4>(my_lo, chunk * 16, i - lo, own, p, sg);
       scrub(s);
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r)
@@ -262,24 +333,27 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
     }
   }
 
-  // ---- phase C: rows
-  for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
-    const size_t row_vec0 = (size_t)row * p.hv;
-    uint4 s[VPT];
+  // ---- rows: wait for the sums, epilogue
+  if (is_row) {
+    for (int row = row0; row < p.tokens; row += row_stride) {
+      const size_t row_vec0 = (size_t)row * p.hv;
+      uint4 s[VPT], res[VPT];
+      load_residual<VPT>(res, row_vec0, p);  // in flight while we wait on the peers
 #pragma unroll
-    for (int j = 0; j < VPT; ++j) {
-      const int c = threadIdx.x + j * blockDim.x;
-      if (c < p.hv) {
-        const size_t idx = row_vec0 + c;
-        if (TWOSHOT) {
-          s[j] = wait_one(my_hi + idx * 16, p, sg);
-        } else {
-          const uint4 own = ld_v4((const char*)p.in + idx * 16);
-          s[j] = gather_sum<T>(my_lo, nvec * 16, idx, own, p, sg);
+      for (int j = 0; j < VPT; ++j) {
+        const int c = threadIdx.x + j * blockDim.x;
+        if (c < p.hv) {
+          const size_t idx = row_vec0 + c;
+          if (TWOSHOT) {
+            s[j] = wait_one(my_hi + idx * 16, p, sg);
+          } else {
+            const uint4 own = ld_v4((const char*)p.in + idx * 16);
+            s[j] = gather_sum<T, 8>(my_lo, nvec * 16, idx, own, p, sg);
+          }
         }
       }
+      row_epilogue<T, VPT>(s, res, gam, row_vec0, p, smem, parity);
     }
-    row_epilogue<T, VPT>(s, row_vec0, p, smem);
   }
 
   finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
@@ -290,6 +364,8 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
 // ---- plain all-reduce (no epilogue): flat vector indexing -----------------------------------------
 template <typename T, bool TWOSHOT>
 __device__ __forceinline__ void ar_body(const RankParams& p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const uint32_t epoch = p.st->epoch;
   const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -300,43 +376,59 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
   char* my_hi = my_lo + p.g.hi_off;
   SpinGuard sg;
 
-  for (size_t idx = gtid; idx < nvec; idx += gsize) {
-    uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
-    scrub(v);
-    if (!TWOSHOT) {
+  const int link_blocks = TWOSHOT ? p.link_blocks : 0;
+  const bool specialised = TWOSHOT && link_blocks > 0 && link_blocks < (int)gridDim.x;
+  const bool is_link = !specialised || (int)blockIdx.x < link_blocks;
+  const bool is_out = !specialised || (int)blockIdx.x >= link_blocks;
+  const size_t ltid = gtid;
+  const size_t lsize = (size_t)(specialised ? link_blocks : gridDim.x) * blockDim.x;
+  const size_t otid = specialised ? gtid - (size_t)link_blocks * blockDim.x : gtid;
+  const size_t osize = specialised ? gsize - (size_t)link_blocks * blockDim.x : gsize;
+
+  if (!TWOSHOT) {
+    for (size_t idx = gtid; idx < nvec; idx += gsize) {
+      uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+      scrub(v);
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r)
         if (r < p.world && r != p.rank)
           st_push_v4(lam_region(p, r, b) + ((size_t)p.rank * nvec + idx) * 16, v);
-    } else {
-      const int owner = (int)(idx / chunk);
-      if (owner != p.rank)
-        st_push_v4(lam_region(p, owner, b) + ((size_t)p.rank * chunk + (idx - owner * chunk)) * 16,
-                   v);
+    }
+  } else if (is_link) {
+    for (int k = 1; k < p.world; ++k) {
+      const int owner = (p.rank + k) % p.world;
+      const size_t lo = (size_t)owner * chunk;
+      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+      if (lo < hi)
+        push_range<4>((const char*)p.in, lam_region(p, owner, b) + (size_t)p.rank * chunk * 16, lo,
+                      hi, ltid, lsize);
     }
   }
-  {
+  if (is_out) {
     char* prev = lam_region(p, p.rank, pb);
-    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
-    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
+    rearm(prev, p.st->dirty_lo[pb], otid, osize);
+    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], otid, osize);
   }
   if (TWOSHOT) {
-    const size_t lo = (size_t)p.rank * chunk;
-    const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-    for (size_t i = lo + gtid; i < hi; i += gsize) {
-      const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
-      uint4 s = gather_sum<T>(my_lo, chunk * 16, i - lo, own, p, sg);
-      scrub(s);
+    if (is_link) {
+      const size_t lo = (size_t)p.rank * chunk;
+      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+      for (size_t i = lo + ltid; i < hi; i += lsize) {
+        const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
+        uint4 s = gather_sum<T, 4>(my_lo, chunk * 16, i - lo, own, p, sg);
+        scrub(s);
 #pragma unroll
-      for (int r = 0; r < kMaxRanks; ++r)
-        if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
+      }
     }
-    for (size_t idx = gtid; idx < nvec; idx += gsize)
-      st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
+    if (is_out)
+      for (size_t idx = otid; idx < nvec; idx += osize)
+        st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
   } else {
     for (size_t idx = gtid; idx < nvec; idx += gsize) {
       const uint4 own = ld_v4((const char*)p.in + idx * 16);
-      st_v4((char*)p.out + idx * 16, gather_sum<T>(my_lo, nvec * 16, idx, own, p, sg));
+      st_v4((char*)p.out + idx * 16, gather_sum<T, 8>(my_lo, nvec * 16, idx, own, p, sg));
     }
   }
   finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
@@ -348,13 +440,13 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512) ar_norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[34];
+  __shared__ float smem[64];
   ar_norm_body<T, VPT, TWOSHOT>(p, smem);
 }
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
-  __shared__ float smem[34];
+  __shared__ float smem[64];
   ar_norm_body<T, VPT, TWOSHOT>(ep.r[blockIdx.y], smem);
 }
 
@@ -372,16 +464,22 @@ __global__ void __launch_bounds__(512) ar_kernel_emu(const __grid_constant__ Emu
 // residual add + RMSNorm on rows of `in` (res_in == nullptr: plain rms_norm).
 template <typename T, int VPT>
 __global__ void __launch_bounds__(512) norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[34];
+  __shared__ float smem[64];
+  pdl_launch_dependents();
+  uint4 gam[VPT];
+  load_gamma<T, VPT>(gam, p);
+  pdl_wait();
+  int parity = 0;
   for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
     const size_t row_vec0 = (size_t)row * p.hv;
-    uint4 s[VPT];
+    uint4 s[VPT], res[VPT];
+    load_residual<VPT>(res, row_vec0, p);
 #pragma unroll
     for (int j = 0; j < VPT; ++j) {
       const int c = threadIdx.x + j * blockDim.x;
       if (c < p.hv) s[j] = ld_stream_v4((const char*)p.in + (row_vec0 + c) * 16);
     }
-    row_epilogue<T, VPT>(s, row_vec0, p, smem);
+    row_epilogue<T, VPT>(s, res, gam, row_vec0, p, smem, parity);
   }
 }
 
