@@ -188,6 +188,28 @@ int b200c_emu_all_gather_lastdim(b200c_ctx* const* ctxs, int world, const void* 
 int b200c_emu_sendrecv(b200c_ctx* const* ctxs, int world, int src, int dst, const void* sendbuf,
                        void* recvbuf, size_t bytes, void* stream);
 
+/* ---- the one entry point that allocates nothing ---------------------------------------------------
+ * No counterpart in the reference.  Same result as b200c_emu_all_reduce, for callers that
+ * must not allocate device memory when they call: code running inside a serving process after
+ * the engine has given all free HBM to its KV-cache pool (a cudaMalloc can fail, and it
+ * escapes the engine's memory accounting and its sleep-mode allocator), or while another
+ * thread is capturing a CUDA graph (cudaMalloc is illegal then).  It needs no ctx and no
+ * arenas: all scratch (every emulated rank's receive regions and state) lives in a
+ * file-scope device array of about 3.6 MiB that each GPU loading this library holds until
+ * the process exits.
+ *   - limit: world <= B200C_MAX_RANKS and numel*sizeof(T) <= B200C_NOALLOC_MAX_BYTES per
+ *     rank (one-shot additionally needs world*bytes <= 2*B200C_NOALLOC_MAX_BYTES); anything
+ *     larger returns B200C_ETOOBIG and launches nothing;
+ *   - the first call on a device resolves the array's device address; make it before any
+ *     stream capture begins;
+ *   - every call re-arms the shared array on `stream` before it runs, because the array
+ *     keeps the previous call's contents; calls whose GPU work may overlap (different
+ *     streams) race on it and must be serialised by the caller;
+ *   - it calls no cudaMalloc, cudaFree or other allocating routine, on any call. */
+#define B200C_NOALLOC_MAX_BYTES (64 * 1024)
+int b200c_emu_all_reduce_noalloc(int world, const void* const* ins, void* const* outs,
+                                 size_t numel, int dtype, int variant, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,6 +21,7 @@ OK, EINVAL, ECUDA, ETOOBIG, ETIMEOUT, ENOMEM = 0, -1, -2, -3, -4, -5
 TUNE_ONESHOT_MAX_BYTES, TUNE_ONESHOT_BLOCKS, TUNE_TWOSHOT_BLOCKS = 1, 2, 3
 TUNE_SPIN_TIMEOUT_MS, TUNE_COPY_BLOCKS = 4, 5
 TUNE_LINK_BLOCKS, TUNE_PDL = 6, 7
+NOALLOC_MAX_BYTES = 64 * 1024
 
 Handle = c_ubyte * IPC_HANDLE_BYTES
 PtrArray = POINTER(c_void_p)
@@ -59,6 +60,8 @@ SIGNATURES = {
                                              c_void_p]),
     "b200c_emu_sendrecv": (c_int, [PtrArray, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,
                                    c_void_p]),
+    "b200c_emu_all_reduce_noalloc": (c_int, [c_int, PtrArray, PtrArray, c_size_t, c_int, c_int,
+                                             c_void_p]),
 }
 
 

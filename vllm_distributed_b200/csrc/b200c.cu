@@ -772,3 +772,132 @@ int b200c_emu_sendrecv(b200c_ctx* const* ctxs, int world, int src, int dst, cons
 }
 
 }  // extern "C"
+
+// ======================= entry point that allocates nothing ==========================================
+//
+// b200c_emu_all_reduce_noalloc() is b200c_emu_all_reduce() for callers that are not allowed
+// to allocate device memory.  Inside an inference server that situation is the normal one
+// once start-up is over: vLLM measures free HBM and hands all of it to the KV-cache pool, so a
+// later cudaMalloc may simply fail; with its sleep-mode (cumem) allocator every allocation has
+// to go through the tracked pool, which a raw cudaMalloc bypasses; and while any thread of the
+// process is capturing a CUDA graph in the default capture mode, cudaMalloc is illegal.  A
+// health check or self-test of the emulated all-reduce that runs in those windows cannot build
+// the usual arenas + per-rank state, so here they live in one file-scope device array.
+//
+// What the caller must know:
+//  * the array is kNoAllocScratchBytes (about 3.6 MiB) of HBM on every GPU that loads this
+//    library, held until the process exits;
+//  * limit: world <= 8 and at most B200C_NOALLOC_MAX_BYTES (64 KiB) per rank and call (the
+//    one-shot variant additionally needs world * bytes <= 128 KiB); larger requests are
+//    rejected with B200C_ETOOBIG and nothing is launched;
+//  * the first call on a device looks the array's device address up (cudaGetSymbolAddress --
+//    in host code the array's name is only a stand-in, never a usable device pointer).  Make
+//    that first call before starting any stream capture;
+//  * all calls share the one array and it keeps whatever the previous call left, so every
+//    call first re-arms, on `stream`, the parts that must start clean (per-rank state to
+//    zero, receive regions to "not arrived").  Two calls whose GPU work can overlap -- on
+//    different streams, or from different threads or processes' worth of streams on the same
+//    device -- race on the array; serialise them;
+//  * no cudaMalloc / cudaFree / allocating library routine is called, on any call.
+namespace {
+
+constexpr size_t kNoAllocMaxBytes = 64 * 1024;
+constexpr size_t kNoAllocHalf = kNoAllocMaxBytes;                    // already 256-aligned
+constexpr size_t kNoAllocArenaBytes = kCtrlBytes + 3 * 2 * kNoAllocHalf + 2 * 256 + kMaxRanks * 2 * 256;
+constexpr size_t kNoAllocStateStride = 256;
+static_assert(sizeof(LocalState) <= kNoAllocStateStride, "LocalState must fit its slot");
+constexpr size_t kNoAllocStateOff = kMaxRanks * kNoAllocArenaBytes;
+constexpr size_t kNoAllocScratchBytes = kNoAllocStateOff + kMaxRanks * kNoAllocStateStride;
+
+constexpr int kNoAllocMaxDevices = 64;
+
+}  // namespace
+
+// File scope, device memory.  Host code may only take its address through
+// cudaGetSymbolAddress; device code in this file could name it directly.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+
+struct NoAllocDevice {
+  char* base = nullptr;  // device address of g_noalloc_scratch on that device
+  int sm_count = 0;
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+
+// Once per device, with that device current.
+int noalloc_setup(int* dev_out, NoAllocDevice** out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(B200C_EINVAL, "device index %d out of range", dev);
+  NoAllocDevice& d = g_noalloc_dev[dev];
+  if (d.base == nullptr) {
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255u) != 0)
+      return fail(B200C_ECUDA, "static scratch has no usable device address");
+    int sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    d.sm_count = sms;
+    d.base = static_cast<char*>(p);
+  }
+  *dev_out = dev;
+  *out = &d;
+  return B200C_OK;
+}
+
+}  // namespace
+
+extern "C" int b200c_emu_all_reduce_noalloc(int world, const void* const* ins, void* const* outs,
+                                            size_t numel, int dtype, int variant, void* stream) {
+  if (world < 2 || world > kMaxRanks) return fail(B200C_EINVAL, "bad emulated world %d", world);
+  if (!ins || !outs) return fail(B200C_EINVAL, "null pointer array");
+  const int es = dtype_size(dtype);
+  if (!es) return fail(B200C_EINVAL, "bad dtype %d", dtype);
+  const size_t bytes = numel * es;
+  if (bytes > kNoAllocMaxBytes)
+    return fail(B200C_ETOOBIG,
+                "message of %zu bytes exceeds the no-allocation limit of %zu bytes per rank", bytes,
+                kNoAllocMaxBytes);
+  int dev = 0;
+  NoAllocDevice* d = nullptr;
+  int rc = noalloc_setup(&dev, &d);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+
+  // Host-side descriptors only (stack objects; nothing here owns device memory).
+  b200c_ctx ctx[kMaxRanks];
+  b200c_ctx* ctxs[kMaxRanks];
+  size_t total = 0;
+  const ArenaGeom geom = make_geom(world, kNoAllocMaxBytes, 16, 16, &total);
+  if (total > kNoAllocArenaBytes) return fail(B200C_EINVAL, "internal: static arena too small");
+  for (int r = 0; r < world; ++r) {
+    ctx[r].rank = r;
+    ctx[r].world = world;
+    ctx[r].device = dev;
+    ctx[r].sm_count = d->sm_count;
+    ctx[r].max_bytes = kNoAllocMaxBytes;
+    ctx[r].geom = geom;
+    for (int q = 0; q < world; ++q) ctx[r].arena[q] = d->base + (size_t)q * kNoAllocArenaBytes;
+    ctx[r].st = reinterpret_cast<LocalState*>(d->base + kNoAllocStateOff + (size_t)r * kNoAllocStateStride);
+    ctx[r].oneshot_blocks = d->sm_count;
+    ctx[r].twoshot_blocks = d->sm_count;
+    // AUTO must only pick one-shot when world copies of the message fit one receive region
+    ctx[r].oneshot_max_bytes =
+        std::min<long long>(ctx[r].oneshot_max_bytes, (long long)(geom.lam_stride / world));
+    ctxs[r] = &ctx[r];
+  }
+  // Validate before touching the array (same rules as the allocating entry point).
+  if (bytes % 16) return fail(B200C_EINVAL, "numel*sizeof(T) = %zu is not a multiple of 16", bytes);
+  if (bytes == 0) return B200C_OK;
+  rc = check_ar_fit(ctxs[0], bytes, pick_variant(ctxs[0], bytes, variant));
+  if (rc) return rc;
+
+  // The array still holds the previous call's traffic: start every rank from call 0 again.
+  CUDA_TRY(cudaMemsetAsync(d->base + kNoAllocStateOff, 0, kMaxRanks * kNoAllocStateStride, s));
+  const size_t arm_vecs = (size_t)world * kNoAllocArenaBytes / 16;
+  fill_not_arrived_kernel<<<std::max(1, d->sm_count), 256, 0, s>>>(
+      reinterpret_cast<uint4*>(d->base), arm_vecs);
+  CUDA_TRY(cudaGetLastError());
+  return ar_impl(ctxs, world, ins, outs, numel, dtype, variant, s);
+}
