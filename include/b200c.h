@@ -54,6 +54,7 @@ extern "C" {
 #define B200C_TUNE_COPY_BLOCKS 5       /* CTAs for all-gather / send / recv          */
 #define B200C_TUNE_LINK_BLOCKS 6       /* two-shot CTAs doing link work; 0 = half the grid */
 #define B200C_TUNE_PDL 7               /* programmatic dependent launch on/off (default on) */
+#define B200C_TUNE_ONESHOT_SPLIT 8     /* CTAs (cluster size) per row, one-shot fused: 0 auto, 1 none */
 
 typedef struct b200c_ctx b200c_ctx;
 

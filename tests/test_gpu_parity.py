@@ -163,6 +163,28 @@ def test_fused_vs_oracle(pkg, world, variant):
     g.check_health()
 
 
+@pytest.mark.parametrize("split", [1, 2, 4, 8])
+def test_fused_oneshot_row_split_variants(pkg, split):
+    """One-shot fused kernel with the row on 1 CTA (no cluster) or split over 2/4/8 cluster CTAs."""
+    _, _, C = pkg
+    g = group(pkg, 4)
+    g.set_tuning(C.TUNE_ONESHOT_SPLIT, split)
+    try:
+        for (t, h) in [(1, 8192), (3, 4096), (40, 8192), (5, 896), (300, 2048), (2, 16384)]:
+            xs = [rand((t, h), torch.bfloat16, 77 + r) for r in range(4)]
+            res, gamma = rand((t, h), torch.bfloat16, 7), rand((h,), torch.bfloat16, 8)
+            y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+            ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs], [res.cuda() for _ in range(4)],
+                                              gamma.cuda(), 1e-5, variant=1)
+            for r in range(4):
+                assert bits_equal(rs[r], r_ref), f"residual, split {split}, shape {(t, h)} rank {r}"
+                assert bits_equal(ys[r], ys[0])
+            check_norm(ys[0], y_ref, torch.bfloat16)
+        g.check_health()
+    finally:
+        g.set_tuning(C.TUNE_ONESHOT_SPLIT, 0)
+
+
 @pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
 def test_fused_other_dtypes(pkg, dtype):
     g = group(pkg, 4)

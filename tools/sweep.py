@@ -21,6 +21,14 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
+# FlashInfer's fused kernel is JIT-built; a copy cross-compiled in the build container (6.5 min of
+# nvcc) travels in baseline/_fi so the GPU box does not spend its lease compiling it.
+_FI = os.path.join(ROOT, "baseline", "_fi")
+if os.path.isdir(_FI):
+    os.environ.setdefault("FLASHINFER_WORKSPACE_BASE", _FI)
+
+import contextlib  # noqa: E402
+
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
@@ -28,8 +36,9 @@ from vllm_distributed_b200 import _cabi as C  # noqa: E402
 from vllm_distributed_b200 import comm as bc  # noqa: E402
 
 
-def time_graph(fn, iters, reps, dev, n):
+def time_graph(fn, iters, reps, dev, n, capture_ctx=None):
     """fn(i) enqueues call i; returns us per call (min over reps, max over ranks)."""
+    capture_ctx = capture_ctx or contextlib.nullcontext
     s = torch.cuda.Stream()
     with torch.cuda.stream(s):
         for i in range(3):
@@ -37,7 +46,7 @@ def time_graph(fn, iters, reps, dev, n):
     torch.cuda.synchronize()
     dist.barrier()
     g = torch.cuda.CUDAGraph()
-    with torch.cuda.stream(s):
+    with torch.cuda.stream(s), capture_ctx():
         with torch.cuda.graph(g, stream=s):
             for i in range(iters):
                 fn(i)
@@ -68,6 +77,7 @@ def main():
     ap.add_argument("--blocks", type=int, nargs="+", default=[148, 296])
     ap.add_argument("--link", type=int, nargs="+", default=[24, 48, 74, 110])
     ap.add_argument("--no-flashinfer", action="store_true")
+    ap.add_argument("--no-vllm-ca", action="store_true")
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
 
@@ -98,6 +108,23 @@ def main():
             if rank == 0:
                 print(f"flashinfer comparator unavailable: {type(e).__name__}: {e}", file=sys.stderr)
 
+    ca = None
+    if not args.no_vllm_ca:
+        try:
+            from vllm.distributed.device_communicators.custom_all_reduce import CustomAllreduce
+            ca = CustomAllreduce(group=cpu, device=dev, max_size=8 << 20)
+            if ca.disabled:
+                ca = None
+            import vllm._custom_ops as vops  # noqa: F401
+        except Exception as e:  # noqa: BLE001
+            ca = None
+            if rank == 0:
+                print(f"vLLM custom all-reduce comparator unavailable: {type(e).__name__}: {e}",
+                      file=sys.stderr)
+    if rank == 0:
+        print(f"comparators: flashinfer={'yes' if fi else 'no'} vllm_custom_ar={'yes' if ca else 'no'}",
+              file=sys.stderr)
+
     rows = []
     tokens = [1 << i for i in range(0, 14) if (1 << i) <= args.max_tokens]
     if args.quick:
@@ -117,12 +144,16 @@ def main():
                 return lambda i: comm.all_reduce_add_rmsnorm_into(xs[i % NBUF], res, gamma, 1e-5,
                                                                  out, variant)
             if S * n <= 2 * max_bytes and S <= (8 << 20):
-                comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 148)
-                for pdl in (1, 0):
-                    comm.set_tuning(C.TUNE_PDL, pdl)
-                    row[f"oneshot_pdl{pdl}_us"] = round(time_graph(ours(C.ONESHOT), iters, 3, dev, n), 2)
+                comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 1184)
+                for split in (0, 1):
+                    comm.set_tuning(C.TUNE_ONESHOT_SPLIT, split)
+                    for pdl in (1, 0):
+                        comm.set_tuning(C.TUNE_PDL, pdl)
+                        row[f"oneshot_split{split}_pdl{pdl}_us"] = round(
+                            time_graph(ours(C.ONESHOT), iters, 3, dev, n), 2)
                 comm.set_tuning(C.TUNE_PDL, 1)
-                row["oneshot_us"] = min(row["oneshot_pdl1_us"], row["oneshot_pdl0_us"])
+                comm.set_tuning(C.TUNE_ONESHOT_SPLIT, 0)
+                row["oneshot_us"] = min(v for k, v in row.items() if k.startswith("oneshot_split"))
             best = None
             for blk in args.blocks:
                 for link in args.link:
@@ -156,6 +187,19 @@ def main():
                 bc.fused_add_rms_norm_(tmp[i % NBUF], res, gamma, 1e-5)
             row["nccl_ar_us"] = round(time_graph(nccl_only, iters, 3, dev, n), 2)
             row["nccl_pair_us"] = round(time_graph(nccl_pair, iters, 3, dev, n), 2)
+
+            if ca is not None and S <= (8 << 20):
+                try:
+                    def ca_only(i):
+                        return ca.custom_all_reduce(xs[i % NBUF])
+
+                    def ca_pair(i):
+                        o = ca.custom_all_reduce(xs[i % NBUF])
+                        torch.ops._C.fused_add_rms_norm(o, res, gamma, 1e-5)
+                    row["vllm_ca_us"] = round(time_graph(ca_only, iters, 3, dev, n, ca.capture), 2)
+                    row["vllm_ca_pair_us"] = round(time_graph(ca_pair, iters, 3, dev, n, ca.capture), 2)
+                except Exception as e:  # noqa: BLE001
+                    row["vllm_ca_error"] = f"{type(e).__name__}: {e}"[:200]
 
             if fi is not None and T > n:  # two-shot asserts token_num > world_size
                 ficomm, ws = fi

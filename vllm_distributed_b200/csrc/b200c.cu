@@ -66,6 +66,7 @@ struct b200c_ctx {
   long long spin_timeout_ms = 10000;
   int link_blocks = 0;  // two-shot CTAs doing link work; 0 = half of the grid
   int pdl = 1;          // programmatic dependent launch on the real (non-emulated) kernels
+  int oneshot_split = 0;  // CTAs per row in the one-shot fused kernel: 0 auto, 1 = no cluster
 };
 
 namespace {
@@ -124,28 +125,68 @@ int coresident_blocks(K kernel, int threads, int sm_count, int* out) {
 
 template <typename K, typename P>
 int launch(K kernel, dim3 grid, int threads, const P& params, cudaStream_t s, bool cooperative,
-           bool pdl = false) {
+           bool pdl = false, int cluster = 1) {
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = grid;
   cfg.blockDim = dim3(threads, 1, 1);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[3];
+  int na = 0;
   if (cooperative) {
-    attr[0].id = cudaLaunchAttributeCooperative;
-    attr[0].val.cooperative = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    attr[na].id = cudaLaunchAttributeCooperative;
+    attr[na].val.cooperative = 1;
+    ++na;
   } else if (pdl) {
     // the kernel may start while its predecessor drains; it blocks in griddepcontrol.wait
     // before touching anything the predecessor produces
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
   }
+  if (cluster > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = na ? attr : nullptr;
+  cfg.numAttrs = na;
   CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, params));
+  return B200C_OK;
+}
+
+// How many clusters of `cluster` CTAs x `threads` threads can be resident at once (cached).
+template <typename K>
+int coresident_clusters(K kernel, int threads, int cluster, int sm_count, int* out) {
+  if (cluster <= 1) return coresident_blocks(kernel, threads, sm_count, out);
+  static thread_local struct { const void* fn; int threads; int cluster; int n; } cache[8] = {};
+  const void* key = reinterpret_cast<const void*>(kernel);
+  for (auto& e : cache)
+    if (e.fn == key && e.threads == threads && e.cluster == cluster) {
+      *out = e.n;
+      return B200C_OK;
+    }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(cluster * sm_count, 1, 1);
+  cfg.blockDim = dim3(threads, 1, 1);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, kernel, &cfg));
+  if (n < 1) return fail(B200C_ECUDA, "no cluster of %d x %d threads can be resident", cluster, threads);
+  static thread_local int next = 0;
+  cache[next] = {key, threads, cluster, n};
+  next = (next + 1) % 8;
+  *out = n;
   return B200C_OK;
 }
 
@@ -228,6 +269,39 @@ int launch_ar_norm_v(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int
   }
 #undef B200C_CASE
   return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
+}
+
+// one-shot fused, rows split over clusters of `split` CTAs
+template <typename T>
+int launch_ar_norm_cluster(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int split,
+                           int threads, int want_groups, cudaStream_t s) {
+  if (nemu == 0) {
+    int cap = 0;
+    int rc = coresident_clusters(ar_norm_cluster_kernel<T>, threads, split, ctxs[0]->sm_count, &cap);
+    if (rc) return rc;
+    const int g = std::max(1, std::min(want_groups, cap));
+    return launch(ar_norm_cluster_kernel<T>, dim3(g * split, 1, 1), threads, rp[0], s, false,
+                  ctxs[0]->pdl != 0, split);
+  }
+  int cap = 0;
+  int rc = coresident_clusters(ar_norm_cluster_kernel_emu<T>, threads, split, ctxs[0]->sm_count, &cap);
+  if (rc) return rc;
+  const int g = std::max(1, std::min(want_groups, cap / nemu));
+  EmuParams ep;
+  memset(&ep, 0, sizeof(ep));
+  for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
+  // Cooperative launch guarantees co-residency of the emulated ranks; if the driver refuses
+  // to combine it with cluster dimensions, launch plainly (the grid was sized to fit).
+  cudaLaunchConfig_t probe;
+  (void)probe;
+  int lrc = launch(ar_norm_cluster_kernel_emu<T>, dim3(g * split, nemu, 1), threads, ep, s, true,
+                   false, split);
+  if (lrc != B200C_OK) {
+    cudaGetLastError();
+    lrc = launch(ar_norm_cluster_kernel_emu<T>, dim3(g * split, nemu, 1), threads, ep, s, false,
+                 false, split);
+  }
+  return lrc;
 }
 
 template <typename T, bool TWOSHOT>
@@ -334,6 +408,21 @@ int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
   int vpt, threads;
   norm_shape(hv, &vpt, &threads);
   const bool two = variant == B200C_TWOSHOT;
+  if (!two && c0->oneshot_split != 1) {
+    // latency regime: one vector per thread, a row spread over up to 8 CTAs of a cluster
+    int split = c0->oneshot_split > 1 ? c0->oneshot_split : (hv + 127) / 128;
+    split = std::max(1, std::min(split, 8));
+    while (split > 1 && (hv + split - 1) / split > 256) ++split;
+    if (split <= 8 && (hv + split - 1) / split <= 256) {
+      const int cthreads = std::max(32, ((hv + split - 1) / split + 31) / 32 * 32);
+      const int want_groups = std::min(tokens, c0->oneshot_blocks);
+      switch (dtype) {
+        case B200C_BF16: return launch_ar_norm_cluster<__nv_bfloat16>(ctxs, nemu, rp, split, cthreads, want_groups, s);
+        case B200C_F16: return launch_ar_norm_cluster<__half>(ctxs, nemu, rp, split, cthreads, want_groups, s);
+        case B200C_F32: return launch_ar_norm_cluster<float>(ctxs, nemu, rp, split, cthreads, want_groups, s);
+      }
+    }
+  }
   const int want = two ? c0->twoshot_blocks : std::min(tokens, c0->oneshot_blocks);
   switch (dtype) {
     case B200C_BF16: return launch_ar_norm_v<__nv_bfloat16>(ctxs, nemu, rp, vpt, threads, two, want, s);
@@ -530,6 +619,7 @@ int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
     case B200C_TUNE_COPY_BLOCKS: c->copy_blocks = (int)std::max<long long>(1, v); break;
     case B200C_TUNE_LINK_BLOCKS: c->link_blocks = (int)std::max<long long>(0, v); break;
     case B200C_TUNE_PDL: c->pdl = v != 0; break;
+    case B200C_TUNE_ONESHOT_SPLIT: c->oneshot_split = (int)std::max<long long>(0, std::min<long long>(8, v)); break;
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;
@@ -545,6 +635,7 @@ int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
     case B200C_TUNE_COPY_BLOCKS: *v = c->copy_blocks; break;
     case B200C_TUNE_LINK_BLOCKS: *v = c->link_blocks; break;
     case B200C_TUNE_PDL: *v = c->pdl; break;
+    case B200C_TUNE_ONESHOT_SPLIT: *v = c->oneshot_split; break;
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;

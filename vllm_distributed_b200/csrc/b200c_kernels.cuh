@@ -180,6 +180,111 @@ __device__ __forceinline__ void push_range(const char* in, char* dst, size_t lo,
   }
 }
 
+// ---- two-shot phase B: reduce my chunk, push the rounded sums into every rank's hi half -----------
+// UB vectors x NP peers are polled together so the local round trips overlap; the (UB, NP)
+// shape is picked from the group size at run time (2 ranks: 4x1, <=4 ranks: 2x3, else 1x7).
+template <typename T, int UB, int NP>
+__device__ __forceinline__ void reduce_gather_range(const RankParams& p, uint32_t b,
+                                                    const char* my_lo, size_t chunk, size_t lo,
+                                                    size_t hi, size_t tid, size_t nthreads,
+                                                    SpinGuard& sg) {
+  constexpr int EPV = VecOps<T>::EPV;
+  const size_t slot_bytes = chunk * 16;
+  for (size_t base = lo + tid; base < hi; base += nthreads * UB) {
+    uint4 own[UB], v[UB][NP];
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const size_t i = base + (size_t)u * nthreads;
+      if (i < hi) own[u] = ld_stream_v4((const char*)p.in + i * 16);
+    }
+    bool pending;
+    do {
+      pending = false;
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        const size_t i = base + (size_t)u * nthreads;
+        if (i < hi) {
+#pragma unroll
+          for (int k = 0; k < NP; ++k) {
+            // peer k of this rank, in rank order with the own rank skipped
+            const int r = k + (k >= p.rank ? 1 : 0);
+            if (r < p.world) v[u][k] = ld_poll_v4(my_lo + (size_t)r * slot_bytes + (i - lo) * 16);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        const size_t i = base + (size_t)u * nthreads;
+        if (i < hi) {
+#pragma unroll
+          for (int k = 0; k < NP; ++k) {
+            const int r = k + (k >= p.rank ? 1 : 0);
+            if (r < p.world) pending |= not_arrived(v[u][k]);
+          }
+        }
+      }
+      if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
+    } while (pending);
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const size_t i = base + (size_t)u * nthreads;
+      if (i < hi) {
+        // fp32 accumulation in rank order 0..N-1: peer slots are in rank order with my own
+        // rank skipped, so my contribution goes in just before peer slot k == rank.  (All
+        // array indices are compile-time constants: nothing is spilled to local memory.)
+        float acc[EPV], f[EPV];
+        bool first = true;
+#pragma unroll
+        for (int k = 0; k <= NP; ++k) {
+          if (k == p.rank) {
+            if (first) {
+              VecOps<T>::to_float(own[u], acc);
+              first = false;
+            } else {
+              VecOps<T>::to_float(own[u], f);
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) acc[e] += f[e];
+            }
+          }
+          if (k < NP) {
+            const int r = k + (k >= p.rank ? 1 : 0);
+            if (r < p.world) {
+              if (first) {
+                VecOps<T>::to_float(v[u][k], acc);
+                first = false;
+              } else {
+                VecOps<T>::to_float(v[u][k], f);
+#pragma unroll
+                for (int e = 0; e < EPV; ++e) acc[e] += f[e];
+              }
+            }
+          }
+        }
+        uint4 s = VecOps<T>::from_float(acc);
+        scrub(s);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
+      }
+    }
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void reduce_gather(const RankParams& p, uint32_t b, const char* my_lo,
+                                              size_t chunk, size_t nvec, size_t tid,
+                                              size_t nthreads, SpinGuard& sg) {
+  const size_t lo = (size_t)p.rank * chunk;
+  const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+  if (lo >= hi) return;
+  if (p.world == 2)
+    reduce_gather_range<T, 4, 1>(p, b, my_lo, chunk, lo, hi, tid, nthreads, sg);
+  else if (p.world <= 4)
+    reduce_gather_range<T, 2, 3>(p, b, my_lo, chunk, lo, hi, tid, nthreads, sg);
+  else
+    reduce_gather_range<T, 1, 7>(p, b, my_lo, chunk, lo, hi, tid, nthreads, sg);
+}
+
 // ---- row epilogue: residual add + RMSNorm ------------------------------------------------------
 // s[j] holds the T-rounded all-reduce sum for vector (tid + j*blockDim) of the row, res[j] the
 // residual vector (prefetched before the wait), gam[j] the weight vector (loaded once per CTA).
@@ -320,18 +425,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   }
 
   // ---- two-shot: reduce my chunk, push the sums to every rank's hi half
-  if (TWOSHOT && is_link) {
-    const size_t lo = (size_t)p.rank * chunk;
-    const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-    for (size_t i = lo + ltid; i < hi; i += lsize) {
-      const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
-      uint4 s = gather_sum<T, 4>(my_lo, chunk * 16, i - lo, own, p, sg);
-      scrub(s);
-#pragma unroll
-      for (int r = 0; r < kMaxRanks; ++r)
-        if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
-    }
-  }
+  if (TWOSHOT && is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
 
   // ---- rows: wait for the sums, epilogue
   if (is_row) {
@@ -359,6 +453,110 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
                                 : (unsigned long long)p.world * nvec * 16,
               TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
+}
+
+// ---- one-shot fused kernel, rows split over a thread-block cluster ----------------------------
+// The latency regime (decode batch 1..64): a row of hv vectors is handled by the P CTAs of a
+// cluster, one vector per thread, so the (N-1) pushes and polls of a row are spread over P SMs
+// and all in flight at once.  The row's sum of squares is combined through distributed shared
+// memory in fixed CTA order (same bits on every rank).  P == 1 degenerates to one CTA per row.
+template <typename T>
+__device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float* smem,
+                                                     float* part /* [2] */) {
+  constexpr int EPV = VecOps<T>::EPV;
+  pdl_launch_dependents();
+  const uint32_t P = cluster_nctarank();
+  const uint32_t cta = cluster_ctarank();
+  const int c = (int)(cta * blockDim.x + threadIdx.x);  // vector index inside the row
+  const bool valid = c < p.hv;
+  uint4 gam = make_uint4(0, 0, 0, 0);
+  if (valid) gam = ld_v4((const char*)p.gamma + (size_t)c * 16);
+  pdl_wait();
+
+  const uint32_t epoch = p.st->epoch;
+  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const size_t nvec = (size_t)p.nvec;
+  const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t gsize = (size_t)gridDim.x * blockDim.x;
+  const int group = (int)(blockIdx.x / P), groups = (int)(gridDim.x / P);
+  char* my_lo = lam_region(p, p.rank, b);
+  SpinGuard sg;
+  int parity = 0;
+
+  // push my rows
+  const size_t slot_off = (size_t)p.rank * nvec * 16;
+  for (int row = group; row < p.tokens; row += groups) {
+    if (valid) {
+      const size_t idx = (size_t)row * p.hv + c;
+      uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+      scrub(v);
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < p.world && r != p.rank) st_push_v4(lam_region(p, r, b) + slot_off + idx * 16, v);
+    }
+  }
+  {
+    char* prev = lam_region(p, p.rank, pb);
+    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
+    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
+  }
+  // rows
+  int pp = 0;
+  for (int row = group; row < p.tokens; row += groups) {
+    const size_t idx = (size_t)row * p.hv + c;
+    float x[EPV];
+    float ss = 0.0f;
+    if (valid) {
+      uint4 res = make_uint4(0, 0, 0, 0);
+      if (p.res_in != nullptr) res = ld_stream_v4((const char*)p.res_in + idx * 16);
+      const uint4 own = ld_v4((const char*)p.in + idx * 16);
+      const uint4 s = gather_sum<T, 8>(my_lo, nvec * 16, idx, own, p, sg);
+      VecOps<T>::to_float(s, x);
+      if (p.res_in != nullptr) {
+        float r[EPV];
+        VecOps<T>::to_float(res, r);
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) x[e] = x[e] + r[e];
+        st_v4((char*)p.res_out + idx * 16, VecOps<T>::from_float(x));
+      }
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) ss += x[e] * x[e];
+    }
+    float total = block_sum(ss, smem, parity);
+    if (P > 1) {
+      if (threadIdx.x == 0) part[pp] = total;
+      cluster_sync_all();
+      total = 0.0f;
+      for (uint32_t q = 0; q < P; ++q) total += ld_dsmem_f32(&part[pp], q);
+      pp ^= 1;
+    }
+    if (valid) {
+      const float rs = 1.0f / sqrtf(total / (float)p.hidden + p.eps);
+      float g[EPV], y[EPV];
+      VecOps<T>::to_float(gam, g);
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) y[e] = VecOps<T>::round_trip(x[e] * rs) * g[e];
+      st_v4((char*)p.norm_out + idx * 16, VecOps<T>::from_float(y));
+    }
+  }
+  // no CTA may exit while a cluster sibling can still read its shared memory
+  if (P > 1) cluster_sync_all();
+  finish_call(p, epoch, (unsigned long long)p.world * nvec * 16, 0ull);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) ar_norm_cluster_kernel(const __grid_constant__ RankParams p) {
+  __shared__ float smem[64];
+  __shared__ float part[2];
+  ar_norm_cluster_body<T>(p, smem, part);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    ar_norm_cluster_kernel_emu(const __grid_constant__ EmuParams ep) {
+  __shared__ float smem[64];
+  __shared__ float part[2];
+  ar_norm_cluster_body<T>(ep.r[blockIdx.y], smem, part);
 }
 
 // ---- plain all-reduce (no epilogue): flat vector indexing -----------------------------------------
@@ -410,18 +608,7 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
     rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], otid, osize);
   }
   if (TWOSHOT) {
-    if (is_link) {
-      const size_t lo = (size_t)p.rank * chunk;
-      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-      for (size_t i = lo + ltid; i < hi; i += lsize) {
-        const uint4 own = ld_stream_v4((const char*)p.in + i * 16);
-        uint4 s = gather_sum<T, 4>(my_lo, chunk * 16, i - lo, own, p, sg);
-        scrub(s);
-#pragma unroll
-        for (int r = 0; r < kMaxRanks; ++r)
-          if (r < p.world) st_push_v4(lam_region(p, r, b) + p.g.hi_off + i * 16, s);
-      }
-    }
+    if (is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
     if (is_out)
       for (size_t idx = otid; idx < nvec; idx += osize)
         st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
