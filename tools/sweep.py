@@ -22,10 +22,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 # FlashInfer's fused kernel is JIT-built; a copy cross-compiled in the build container (6.5 min of
-# nvcc) travels in baseline/_fi so the GPU box does not spend its lease compiling it.
-_FI = os.path.join(ROOT, "baseline", "_fi")
-if os.path.isdir(_FI):
-    os.environ.setdefault("FLASHINFER_WORKSPACE_BASE", _FI)
+# nvcc, `gen_trtllm_comm_module().build()` with FLASHINFER_CUDA_ARCH_LIST=10.0a) travels in
+# baseline/_fi/aot and is loaded as a prebuilt module, so the GPU box does not spend its lease
+# compiling the comparator.
+_FI_AOT = os.path.join(ROOT, "baseline", "_fi", "aot")
+
+
+def _use_prebuilt_flashinfer():
+    if os.path.isdir(_FI_AOT):
+        import pathlib
+        from flashinfer.jit import env as jit_env
+        jit_env.FLASHINFER_AOT_DIR = pathlib.Path(_FI_AOT)
+
 
 import contextlib  # noqa: E402
 
@@ -96,6 +104,7 @@ def main():
     fi = None
     if not args.no_flashinfer:
         try:
+            _use_prebuilt_flashinfer()
             import flashinfer.comm as ficomm
             t0 = time.time()
             ws = ficomm.create_allreduce_fusion_workspace(

@@ -412,6 +412,11 @@ int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
     // latency regime: one vector per thread, a row spread over up to 8 CTAs of a cluster
     int split = c0->oneshot_split > 1 ? c0->oneshot_split : (hv + 127) / 128;
     split = std::max(1, std::min(split, 8));
+    if (c0->oneshot_split == 0) {
+      // splitting pays while all tokens x split CTAs are resident at once (about 2 per SM);
+      // beyond that one wider CTA per row is faster (measured, tools/sweep.py)
+      while (split > 1 && (long long)tokens * split > 2LL * c0->sm_count) split >>= 1;
+    }
     while (split > 1 && (hv + split - 1) / split > 256) ++split;
     if (split <= 8 && (hv + split - 1) / split <= 256) {
       const int cthreads = std::max(32, ((hv + split - 1) / split + 31) / 32 * 32);

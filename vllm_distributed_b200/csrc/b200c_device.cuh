@@ -227,14 +227,12 @@ __device__ __forceinline__ uint32_t cluster_nctarank() {
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// read a float from the same shared-memory variable of CTA `rank` of this cluster (DSMEM)
-__device__ __forceinline__ float ld_dsmem_f32(const float* local_smem_ptr, uint32_t rank) {
+// write a float into the same shared-memory variable of CTA `rank` of this cluster (DSMEM)
+__device__ __forceinline__ void st_dsmem_f32(float* local_smem_ptr, uint32_t rank, float v) {
   const uint32_t local = (uint32_t)__cvta_generic_to_shared(local_smem_ptr);
   uint32_t remote;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rank));
-  float v;
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
-  return v;
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
 }
 
 // ---- programmatic dependent launch (no-ops when the launch did not ask for it) -----------------

@@ -138,21 +138,38 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
   for (size_t i = gtid; i < n; i += gsize) st_v4(base + i * 16, m);
 }
 
-// End-of-kernel bookkeeping: the last CTA of this rank publishes the next epoch.
-__device__ __forceinline__ void finish_call(const RankParams& p, uint32_t epoch,
-                                            unsigned long long dlo, unsigned long long dhi) {
-  __syncthreads();
+// Call bookkeeping without an end-of-kernel rendezvous.  Thread 0 of every CTA reads the epoch,
+// fences, and only then takes a ticket; the CTA holding the LAST ticket therefore knows that
+// every CTA of this rank has already read the epoch, and may publish epoch+1 (and the extents
+// this call dirties) whenever it likes -- the value is only consumed by the next kernel.  The
+// ticket's return value is not needed until the end, so its latency is off the critical path.
+struct CallState {
+  uint32_t epoch;
+  uint32_t ticket;  // meaningful in thread 0 only
+};
+
+__device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* s_epoch) {
+  CallState cs;
+  cs.ticket = 0;
   if (threadIdx.x == 0) {
+    const uint32_t e = ld_volatile_u32(&p.st->epoch);
+    *s_epoch = e;
     __threadfence();
-    const uint32_t prev = atomicAdd(&p.st->arrive, 1u);
-    if (prev == gridDim.x - 1) {
-      const uint32_t b = epoch % 3u;
-      p.st->dirty_lo[b] = dlo;
-      p.st->dirty_hi[b] = dhi;
-      p.st->arrive = 0;
-      __threadfence();
-      p.st->epoch = epoch + 1;
-    }
+    cs.ticket = atomicAdd(&p.st->arrive, 1u);
+  }
+  __syncthreads();
+  cs.epoch = *s_epoch;
+  return cs;
+}
+
+__device__ __forceinline__ void end_call(const RankParams& p, const CallState& cs,
+                                         unsigned long long dlo, unsigned long long dhi) {
+  if (threadIdx.x == 0 && cs.ticket == gridDim.x - 1) {
+    const uint32_t b = cs.epoch % 3u;
+    p.st->dirty_lo[b] = dlo;
+    p.st->dirty_hi[b] = dhi;
+    p.st->arrive = 0;
+    p.st->epoch = cs.epoch + 1;
   }
 }
 
@@ -367,7 +384,8 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   load_gamma<T, VPT>(gam, p);  // weights: safe to read before the previous kernel has finished
   pdl_wait();
 
-  const uint32_t epoch = p.st->epoch;
+  const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
+  const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
   const size_t nvec = (size_t)p.nvec;
   const size_t chunk = (nvec + p.world - 1) / p.world;  // two-shot: vectors owned per rank
@@ -450,9 +468,9 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
     }
   }
 
-  finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
-                                : (unsigned long long)p.world * nvec * 16,
-              TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
+  end_call(p, cs, TWOSHOT ? (unsigned long long)p.world * chunk * 16
+                            : (unsigned long long)p.world * nvec * 16,
+           TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
 }
 
 // ---- one-shot fused kernel, rows split over a thread-block cluster ----------------------------
@@ -462,7 +480,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
 // memory in fixed CTA order (same bits on every rank).  P == 1 degenerates to one CTA per row.
 template <typename T>
 __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float* smem,
-                                                     float* part /* [2] */) {
+                                                     float (*part)[kMaxRanks] /* [2][8] */) {
   constexpr int EPV = VecOps<T>::EPV;
   pdl_launch_dependents();
   const uint32_t P = cluster_nctarank();
@@ -473,12 +491,17 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
   if (valid) gam = ld_v4((const char*)p.gamma + (size_t)c * 16);
   pdl_wait();
 
-  const uint32_t epoch = p.st->epoch;
+  const int group = (int)(blockIdx.x / P), groups = (int)(gridDim.x / P);
+  // first row's input is requested before the epoch round trip returns
+  uint4 v0 = make_uint4(0, 0, 0, 0);
+  if (valid && group < p.tokens)
+    v0 = ld_stream_v4((const char*)p.in + ((size_t)group * p.hv + c) * 16);
+  const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
+  const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
   const size_t nvec = (size_t)p.nvec;
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
-  const int group = (int)(blockIdx.x / P), groups = (int)(gridDim.x / P);
   char* my_lo = lam_region(p, p.rank, b);
   SpinGuard sg;
   int parity = 0;
@@ -488,8 +511,9 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
   for (int row = group; row < p.tokens; row += groups) {
     if (valid) {
       const size_t idx = (size_t)row * p.hv + c;
-      uint4 v = ld_stream_v4((const char*)p.in + idx * 16);
+      uint4 v = (row == group) ? v0 : ld_stream_v4((const char*)p.in + idx * 16);
       scrub(v);
+      if (row == group) v0 = v;
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r)
         if (r < p.world && r != p.rank) st_push_v4(lam_region(p, r, b) + slot_off + idx * 16, v);
@@ -500,7 +524,10 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
     rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
     rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
   }
-  // rows
+  // every CTA of the cluster must be running before its shared memory is written remotely;
+  // this wait overlaps the fabric flight time of the pushes
+  if (P > 1) cluster_sync_all();
+
   int pp = 0;
   for (int row = group; row < p.tokens; row += groups) {
     const size_t idx = (size_t)row * p.hv + c;
@@ -509,7 +536,8 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
     if (valid) {
       uint4 res = make_uint4(0, 0, 0, 0);
       if (p.res_in != nullptr) res = ld_stream_v4((const char*)p.res_in + idx * 16);
-      const uint4 own = ld_v4((const char*)p.in + idx * 16);
+      // scrubbing only rewrites -0.0 words to +0.0, so the pushed copy is as good as the input
+      const uint4 own = (row == group) ? v0 : ld_v4((const char*)p.in + idx * 16);
       const uint4 s = gather_sum<T, 8>(my_lo, nvec * 16, idx, own, p, sg);
       VecOps<T>::to_float(s, x);
       if (p.res_in != nullptr) {
@@ -524,10 +552,13 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
     }
     float total = block_sum(ss, smem, parity);
     if (P > 1) {
-      if (threadIdx.x == 0) part[pp] = total;
+      // each CTA deposits its partial in slot [cta] of every sibling (DSMEM stores), then one
+      // cluster barrier; afterwards everybody sums its OWN copy in CTA order.  No CTA reads
+      // remote memory, so nobody has to wait for siblings before exiting.
+      if (threadIdx.x < P) st_dsmem_f32(&part[pp][cta], threadIdx.x, total);
       cluster_sync_all();
       total = 0.0f;
-      for (uint32_t q = 0; q < P; ++q) total += ld_dsmem_f32(&part[pp], q);
+      for (uint32_t q = 0; q < P; ++q) total += part[pp][q];
       pp ^= 1;
     }
     if (valid) {
@@ -539,32 +570,32 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
       st_v4((char*)p.norm_out + idx * 16, VecOps<T>::from_float(y));
     }
   }
-  // no CTA may exit while a cluster sibling can still read its shared memory
-  if (P > 1) cluster_sync_all();
-  finish_call(p, epoch, (unsigned long long)p.world * nvec * 16, 0ull);
+  end_call(p, cs, (unsigned long long)p.world * nvec * 16, 0ull);
 }
 
 template <typename T>
 __global__ void __launch_bounds__(256) ar_norm_cluster_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[64];
-  __shared__ float part[2];
+  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float part[2][kMaxRanks];
   ar_norm_cluster_body<T>(p, smem, part);
 }
 
 template <typename T>
 __global__ void __launch_bounds__(256)
     ar_norm_cluster_kernel_emu(const __grid_constant__ EmuParams ep) {
-  __shared__ float smem[64];
-  __shared__ float part[2];
+  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float part[2][kMaxRanks];
   ar_norm_cluster_body<T>(ep.r[blockIdx.y], smem, part);
 }
 
 // ---- plain all-reduce (no epilogue): flat vector indexing -----------------------------------------
 template <typename T, bool TWOSHOT>
 __device__ __forceinline__ void ar_body(const RankParams& p) {
+  __shared__ uint32_t s_epoch;
   pdl_launch_dependents();
   pdl_wait();
-  const uint32_t epoch = p.st->epoch;
+  const CallState cs = begin_call(p, &s_epoch);
+  const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
@@ -618,22 +649,22 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
       st_v4((char*)p.out + idx * 16, gather_sum<T, 8>(my_lo, nvec * 16, idx, own, p, sg));
     }
   }
-  finish_call(p, epoch, TWOSHOT ? (unsigned long long)p.world * chunk * 16
-                                : (unsigned long long)p.world * nvec * 16,
-              TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
+  end_call(p, cs, TWOSHOT ? (unsigned long long)p.world * chunk * 16
+                            : (unsigned long long)p.world * nvec * 16,
+           TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
 }
 
 // ---- kernels: a real launch carries one rank, an emulated launch carries all of them ----------
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512) ar_norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[64];
+  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
   ar_norm_body<T, VPT, TWOSHOT>(p, smem);
 }
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
-  __shared__ float smem[64];
+  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
   ar_norm_body<T, VPT, TWOSHOT>(ep.r[blockIdx.y], smem);
 }
 
@@ -651,7 +682,7 @@ __global__ void __launch_bounds__(512) ar_kernel_emu(const __grid_constant__ Emu
 // residual add + RMSNorm on rows of `in` (res_in == nullptr: plain rms_norm).
 template <typename T, int VPT>
 __global__ void __launch_bounds__(512) norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[64];
+  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
   pdl_launch_dependents();
   uint4 gam[VPT];
   load_gamma<T, VPT>(gam, p);
