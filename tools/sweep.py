@@ -86,6 +86,7 @@ def main():
     ap.add_argument("--link", type=int, nargs="+", default=[24, 48, 74, 110])
     ap.add_argument("--no-flashinfer", action="store_true")
     ap.add_argument("--no-vllm-ca", action="store_true")
+    ap.add_argument("--pdl", type=int, nargs="+", default=[1, 0])
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
 
@@ -156,7 +157,7 @@ def main():
                 comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 1184)
                 for split in (0, 1):
                     comm.set_tuning(C.TUNE_ONESHOT_SPLIT, split)
-                    for pdl in (1, 0):
+                    for pdl in args.pdl:
                         comm.set_tuning(C.TUNE_PDL, pdl)
                         row[f"oneshot_split{split}_pdl{pdl}_us"] = round(
                             time_graph(ours(C.ONESHOT), iters, 3, dev, n), 2)

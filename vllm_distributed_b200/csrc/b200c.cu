@@ -576,6 +576,9 @@ int b200c_init(int rank, int world, void* const* arena_ptrs, size_t max_bytes, s
   }
   c->oneshot_blocks = c->sm_count;
   c->twoshot_blocks = c->sm_count;
+  // one-shot / two-shot crossover measured on 8 x B200 (tools/sweep.py, profiles/): the more
+  // ranks, the sooner (N-1)*S of one-shot link traffic costs more than a second fabric hop
+  c->oneshot_max_bytes = world <= 2 ? (2 << 20) : world <= 4 ? (1 << 20) : (384 << 10);
   if (world > 1) {
     c->max_bytes = max_bytes;
     c->ag_bytes = ag_bytes;

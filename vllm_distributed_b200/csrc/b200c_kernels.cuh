@@ -25,8 +25,7 @@ struct ArenaGeom {
 // Private (not peer-visible) per-rank device state.  Lives in device memory so that a
 // captured CUDA graph replays correctly: the kernels advance it themselves.
 struct LocalState {
-  uint32_t epoch;        // all-reduce call counter; region = epoch % 3
-  uint32_t arrive;       // CTA arrival counter (end-of-kernel bookkeeping)
+  unsigned long long call;  // (epoch << 32) | tickets taken in the running call; region = epoch % 3
   uint32_t error;        // sticky: 1 = a wait on a peer timed out
   uint32_t ag_seq;       // all-gather call counter
   uint32_t ag_arrive_push;
@@ -138,11 +137,11 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
   for (size_t i = gtid; i < n; i += gsize) st_v4(base + i * 16, m);
 }
 
-// Call bookkeeping without an end-of-kernel rendezvous.  Thread 0 of every CTA reads the epoch,
-// fences, and only then takes a ticket; the CTA holding the LAST ticket therefore knows that
-// every CTA of this rank has already read the epoch, and may publish epoch+1 (and the extents
-// this call dirties) whenever it likes -- the value is only consumed by the next kernel.  The
-// ticket's return value is not needed until the end, so its latency is off the critical path.
+// Call bookkeeping without an end-of-kernel rendezvous and without a fence: the epoch and the
+// tickets of the running call share one 64-bit word, so thread 0 of every CTA learns the epoch
+// and takes its ticket with ONE atomic.  The CTA holding the last ticket knows that every CTA of
+// this rank has already read the epoch and may publish (epoch+1, 0 tickets) and the extents
+// this call dirties whenever it likes -- the next kernel is the only reader.
 struct CallState {
   uint32_t epoch;
   uint32_t ticket;  // meaningful in thread 0 only
@@ -152,10 +151,9 @@ __device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* s
   CallState cs;
   cs.ticket = 0;
   if (threadIdx.x == 0) {
-    const uint32_t e = ld_volatile_u32(&p.st->epoch);
-    *s_epoch = e;
-    __threadfence();
-    cs.ticket = atomicAdd(&p.st->arrive, 1u);
+    const unsigned long long w = atomicAdd(&p.st->call, 1ull);
+    cs.ticket = (uint32_t)w;
+    *s_epoch = (uint32_t)(w >> 32);
   }
   __syncthreads();
   cs.epoch = *s_epoch;
@@ -168,8 +166,7 @@ __device__ __forceinline__ void end_call(const RankParams& p, const CallState& c
     const uint32_t b = cs.epoch % 3u;
     p.st->dirty_lo[b] = dlo;
     p.st->dirty_hi[b] = dhi;
-    p.st->arrive = 0;
-    p.st->epoch = cs.epoch + 1;
+    p.st->call = (unsigned long long)(cs.epoch + 1) << 32;
   }
 }
 
@@ -192,6 +189,39 @@ __device__ __forceinline__ void push_range(const char* in, char* dst, size_t lo,
       if (i < hi) {
         scrub(v[u]);
         st_push_v4(dst + (i - lo) * 16, v[u]);
+      }
+    }
+  }
+}
+
+// Two-shot scatter: for each offset inside a chunk, the N-1 vectors bound for the N-1 peers
+// are loaded together and pushed together, so every peer link is fed at the same time and a
+// small message costs one load round trip instead of one per peer.  Slot k is the k-th peer to
+// the right of this rank.
+__device__ __forceinline__ void scatter_chunks(const RankParams& p, uint32_t b, size_t chunk,
+                                               size_t nvec, size_t tid, size_t nthreads) {
+  const size_t slot = (size_t)p.rank * chunk * 16;
+  for (size_t off = tid; off < chunk; off += nthreads) {
+    uint4 v[kMaxRanks - 1];
+#pragma unroll
+    for (int k = 0; k < kMaxRanks - 1; ++k) {
+      if (k + 1 < p.world) {
+        int owner = p.rank + k + 1;
+        owner = owner >= p.world ? owner - p.world : owner;
+        const size_t idx = (size_t)owner * chunk + off;
+        if (idx < nvec) v[k] = ld_stream_v4((const char*)p.in + idx * 16);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kMaxRanks - 1; ++k) {
+      if (k + 1 < p.world) {
+        int owner = p.rank + k + 1;
+        owner = owner >= p.world ? owner - p.world : owner;
+        const size_t idx = (size_t)owner * chunk + off;
+        if (idx < nvec) {
+          scrub(v[k]);
+          st_push_v4(lam_region(p, owner, b) + slot + off * 16, v[k]);
+        }
       }
     }
   }
@@ -423,16 +453,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
       }
     }
   } else if (is_link) {
-    // scatter: peer after peer, each rank starting at its right-hand neighbour so that at any
-    // moment the N ranks write to N different destinations
-    for (int k = 1; k < p.world; ++k) {
-      const int owner = (p.rank + k) % p.world;
-      const size_t lo = (size_t)owner * chunk;
-      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-      if (lo < hi)
-        push_range<4>((const char*)p.in, lam_region(p, owner, b) + (size_t)p.rank * chunk * 16, lo,
-                      hi, ltid, lsize);
-    }
+    scatter_chunks(p, b, chunk, nvec, ltid, lsize);
   }
 
   // ---- re-arm the previous call's region while the pushes are in flight
@@ -624,14 +645,7 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
           st_push_v4(lam_region(p, r, b) + ((size_t)p.rank * nvec + idx) * 16, v);
     }
   } else if (is_link) {
-    for (int k = 1; k < p.world; ++k) {
-      const int owner = (p.rank + k) % p.world;
-      const size_t lo = (size_t)owner * chunk;
-      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
-      if (lo < hi)
-        push_range<4>((const char*)p.in, lam_region(p, owner, b) + (size_t)p.rank * chunk * 16, lo,
-                      hi, ltid, lsize);
-    }
+    scatter_chunks(p, b, chunk, nvec, ltid, lsize);
   }
   if (is_out) {
     char* prev = lam_region(p, p.rank, pb);
