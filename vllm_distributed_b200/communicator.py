@@ -1,0 +1,123 @@
+"""B200Communicator: drop-in for vLLM's CudaCommunicator on the TP / PP hot path.
+
+Mirrors the interface GroupCoordinator drives (vllm/distributed/parallel_state.py:538-616,
+1061-1091): all_reduce, all_gather, send, recv, destroy -- same names, argument meaning and
+error behaviour as vllm/distributed/device_communicators/cuda_communicator.py:241-420 and
+base_device_communicator.py:184-300.  It subclasses CudaCommunicator because
+GroupCoordinator.graph_capture asserts the type (parallel_state.py:489-496); everything it
+does not take (non-contiguous or odd-sized tensors, messages beyond the arena, groups that
+span hosts, groups that are neither TP nor PP) goes to the parent class unchanged.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+from vllm.distributed.device_communicators.cuda_communicator import CudaCommunicator
+from vllm.logger import init_logger
+
+from . import _cabi as C
+from .comm import (DEFAULT_AG_BYTES, DEFAULT_MAX_BYTES, DEFAULT_P2P_BYTES, B200Comm)
+
+logger = init_logger(__name__)
+
+
+def _group_kind(unique_name: str) -> str:
+    return unique_name.split(":")[0]
+
+
+class B200Communicator(CudaCommunicator):
+    def __init__(self, cpu_group, device=None, device_group=None, unique_name: str = "", **kw):
+        super().__init__(cpu_group, device, device_group, unique_name, **kw)
+        self.b200: B200Comm | None = None
+        C.lib()  # a missing libb200c.so is an error, never a silent NCCL run
+        kind = _group_kind(unique_name)
+        if self.world_size < 2 or self.world_size > C.MAX_RANKS or kind not in ("tp", "pp"):
+            return
+        if os.environ.get("B200C_DISABLE", "0") == "1":
+            return
+        from vllm.distributed.parallel_state import in_the_same_node_as
+        if not all(in_the_same_node_as(cpu_group, source_rank=0)):
+            # the reference launcher keeps a TP group on one host (launch.py:213-240); PP hops
+            # between hosts stay on NCCL exactly as in the reference
+            logger.info("b200c: group %s spans hosts, using the stock communicator", unique_name)
+            return
+        if kind == "tp":
+            sizes = dict(max_bytes=DEFAULT_MAX_BYTES, ag_bytes=DEFAULT_AG_BYTES, p2p_bytes=1 << 20)
+        else:
+            sizes = dict(max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=DEFAULT_P2P_BYTES)
+        self.b200 = B200Comm.from_process_group(cpu_group, self.device, **sizes)
+        logger.info("b200c: %s group of %d ranks on NVLink arenas (%s)", kind, self.world_size,
+                    ", ".join(f"{k}={v >> 20} MiB" for k, v in sizes.items()))
+
+    # ---- a1..a5: all-reduce -------------------------------------------------------------------
+    def all_reduce(self, input_: torch.Tensor) -> torch.Tensor:
+        b = self.b200
+        if b is not None and b.can_all_reduce(input_):
+            return b.all_reduce(input_)
+        return super().all_reduce(input_)
+
+    # ---- a6..a9: fused all-reduce + residual + RMSNorm ---------------------------------------
+    def can_fuse_norm(self, x: torch.Tensor) -> bool:
+        return self.b200 is not None and x.dim() >= 2 and self.b200.can_fuse_norm(x)
+
+    def all_reduce_add_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor | None,
+                               weight: torch.Tensor, eps: float,
+                               inplace: bool = True) -> tuple[torch.Tensor, torch.Tensor | None]:
+        """(norm_out, residual_out) = fused_add_rms_norm(all_reduce(x), residual, weight, eps).
+        With inplace=True x becomes norm_out and residual is updated, like the reference's
+        flashinfer_trtllm_fused_allreduce_norm (allreduce_rms_fusion.py:121-212)."""
+        if self.can_fuse_norm(x) and weight.dtype == x.dtype and weight.is_contiguous():
+            return self.b200.all_reduce_add_rmsnorm(x, residual, weight, eps, inplace=inplace)
+        # unfused path: the parent's all-reduce and this library's local norm kernels
+        from .comm import fused_add_rms_norm_, rms_norm
+        ar = self.all_reduce(x)
+        if residual is None:
+            return rms_norm(ar, weight, eps), None
+        if not inplace:
+            residual = residual.clone()
+        fused_add_rms_norm_(ar, residual, weight, eps)
+        return ar, residual
+
+    # ---- a10..a11: lm_head logits gather ------------------------------------------------------
+    def all_gather(self, input_: torch.Tensor, dim: int = -1) -> torch.Tensor:
+        b = self.b200
+        if dim < 0:
+            dim += input_.dim()
+        if (b is not None and input_.dim() >= 1 and dim == input_.dim() - 1
+                and b.can_all_gather_lastdim(input_)):
+            return b.all_gather_lastdim(input_)
+        if b is not None and dim == 0 and input_.is_contiguous() and input_.numel() > 0:
+            # dim-0 gather (the PP re-assembly, parallel_state.py:1014-1038) is the last-dim
+            # gather of the flattened tensor viewed as one row
+            flat = input_.reshape(1, -1)
+            if b.can_all_gather_lastdim(flat):
+                out = b.all_gather_lastdim(flat)
+                return out.reshape((self.world_size * input_.shape[0],) + tuple(input_.shape[1:]))
+        return super().all_gather(input_, dim)
+
+    # ---- a12..a13: pipeline hop ------------------------------------------------------------------
+    def send(self, tensor: torch.Tensor, dst: int | None = None) -> None:
+        if dst is None:
+            dst = (self.rank_in_group + 1) % self.world_size
+        b = self.b200
+        if b is not None and b.can_p2p(tensor):
+            b.send(tensor, dst)
+            return
+        super().send(tensor, dst)
+
+    def recv(self, size: torch.Size, dtype: torch.dtype, src: int | None = None) -> torch.Tensor:
+        if src is None:
+            src = (self.rank_in_group - 1) % self.world_size
+        b = self.b200
+        if b is not None:
+            tensor = torch.empty(size, dtype=dtype, device=self.device)
+            if b.can_p2p(tensor):
+                return b.recv(tensor, src)
+        return super().recv(size, dtype, src)
+
+    def destroy(self):
+        if self.b200 is not None:
+            self.b200.close()
+            self.b200 = None
+        super().destroy()

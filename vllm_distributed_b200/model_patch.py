@@ -1,0 +1,108 @@
+"""Eager/compiled fused path for the decoder families BASELINE.json names (Llama, Qwen2).
+
+The reference gets its fused all-reduce + residual + RMSNorm from a torch.compile pattern
+rewrite (vllm/compilation/passes/fusion/allreduce_rms_fusion.py:347-416).  Here the same pairing
+is made at the layer: the row-parallel projections (o_proj, down_proj;
+vllm/model_executor/layers/linear.py:1558-1561) keep their partial sums, and the RMSNorm that
+follows (vllm/model_executor/models/llama.py:316-333, qwen2.py:292-312) is replaced by ONE call of
+torch.ops.vllm.b200c_allreduce_add_rmsnorm, which works eagerly, under Dynamo and inside CUDA
+graphs.  The last layer of every pipeline stage still reduces normally, so the final norm and
+the PP hand-off (llama.py:425-430) see ordinary tensors.
+"""
+from __future__ import annotations
+
+import functools
+
+import torch
+
+_APPLIED = False
+
+
+def _tp():
+    from vllm.distributed.parallel_state import get_tp_group
+    return get_tp_group()
+
+
+def _fusable_norm(norm) -> bool:
+    return (getattr(norm, "has_weight", True) and getattr(norm, "variance_size_override", None) is None
+            and isinstance(getattr(norm, "weight", None), torch.Tensor))
+
+
+def _layer_forward(self, positions, hidden_states, residual, **kwargs):
+    if not getattr(self, "_b200c_fused", False):
+        return self._b200c_orig_forward(positions, hidden_states, residual, **kwargs)
+    group_name = self._b200c_group
+    if residual is None:
+        residual = hidden_states
+        hidden_states = self.input_layernorm(hidden_states)
+    elif self._b200c_input_partial:
+        w = self.input_layernorm
+        torch.ops.vllm.b200c_allreduce_add_rmsnorm(hidden_states, residual, w.weight.data,
+                                                   w.variance_epsilon, group_name)
+    else:
+        hidden_states, residual = self.input_layernorm(hidden_states, residual)
+    hidden_states = self.self_attn(positions=positions, hidden_states=hidden_states, **kwargs)
+    w = self.post_attention_layernorm
+    torch.ops.vllm.b200c_allreduce_add_rmsnorm(hidden_states, residual, w.weight.data,
+                                               w.variance_epsilon, group_name)
+    hidden_states = self.mlp(hidden_states)
+    return hidden_states, residual
+
+
+def _configure_model(model) -> None:
+    """Decide, per layer of this pipeline stage, which all-reduces are deferred into the norm."""
+    tp = _tp()
+    comm = tp.device_communicator
+    if tp.world_size < 2 or comm is None or getattr(comm, "b200", None) is None:
+        return
+    start, end = getattr(model, "start_layer", 0), getattr(model, "end_layer", len(model.layers))
+    layers = list(model.layers)[start:end]
+    for i, layer in enumerate(layers):
+        ok = (hasattr(layer, "self_attn") and hasattr(layer.self_attn, "o_proj")
+              and hasattr(layer, "mlp") and hasattr(layer.mlp, "down_proj")
+              and _fusable_norm(layer.input_layernorm)
+              and _fusable_norm(layer.post_attention_layernorm)
+              and layer.self_attn.o_proj.reduce_results and layer.mlp.down_proj.reduce_results
+              and layer.self_attn.o_proj.bias is None and layer.mlp.down_proj.bias is None)
+        if not ok:
+            # an un-fusable layer must receive a reduced input: un-defer the previous one
+            if i > 0 and getattr(layers[i - 1], "_b200c_fused", False):
+                layers[i - 1].mlp.down_proj.reduce_results = True
+            continue
+        layer._b200c_fused = True
+        layer._b200c_group = tp.unique_name
+        prev_defers = i > 0 and getattr(layers[i - 1], "_b200c_fused", False) and \
+            not layers[i - 1].mlp.down_proj.reduce_results
+        layer._b200c_input_partial = prev_defers
+        layer.self_attn.o_proj.reduce_results = False
+        # the last layer of the stage hands a reduced tensor to the final norm / the PP send
+        layer.mlp.down_proj.reduce_results = (i == len(layers) - 1)
+
+
+def _wrap_model_init(model_cls) -> None:
+    orig_init = model_cls.__init__
+
+    @functools.wraps(orig_init)
+    def init(self, *args, **kwargs):
+        orig_init(self, *args, **kwargs)
+        try:
+            _configure_model(self)
+        except Exception:  # never take the server down for the optimisation
+            import logging
+            logging.getLogger(__name__).exception("b200c: layer fusion disabled")
+    model_cls.__init__ = init
+
+
+def apply() -> None:
+    global _APPLIED
+    if _APPLIED:
+        return
+    _APPLIED = True
+    from vllm.model_executor.models import llama, qwen2
+    for mod, layer_name, model_name in ((llama, "LlamaDecoderLayer", "LlamaModel"),
+                                        (qwen2, "Qwen2DecoderLayer", "Qwen2Model")):
+        layer_cls = getattr(mod, layer_name)
+        if not hasattr(layer_cls, "_b200c_orig_forward"):
+            layer_cls._b200c_orig_forward = layer_cls.forward
+            layer_cls.forward = _layer_forward
+        _wrap_model_init(getattr(mod, model_name))

@@ -1,0 +1,76 @@
+"""vLLM plugin: selects B200Communicator and wires the fused paths (the drop-in seam).
+
+`register()` is the `vllm.general_plugins` entry point (vllm/plugins/__init__.py:69-82); vLLM
+calls it in every process, including the workers the reference launcher starts
+(vllm/v1/worker/worker_base.py:245-247; the launcher forwards VLLM_PLUGINS,
+/root/reference/src/launch.py:198-208).  It is idempotent.
+"""
+
+import os
+
+_DONE = False
+COMM_QUALNAME = "vllm_distributed_b200.communicator.B200Communicator"
+
+
+def _register_fused_op() -> None:
+    """torch.ops.vllm.b200c_allreduce_add_rmsnorm(allreduce_in, residual, weight, eps, group):
+    in place, allreduce_in becomes the normalised output -- the same contract as the reference's
+    flashinfer_trtllm_fused_allreduce_norm (allreduce_rms_fusion.py:121-245)."""
+    import torch
+    from vllm.utils.torch_utils import direct_register_custom_op
+
+    if hasattr(torch.ops.vllm, "b200c_allreduce_add_rmsnorm"):
+        return
+
+    def op(allreduce_in: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, eps: float,
+           group_name: str) -> None:
+        from vllm.distributed.parallel_state import _groups
+        group = _groups[group_name]()
+        if group is None:
+            raise ValueError(f"Group {group_name} is destroyed.")
+        comm = group.device_communicator
+        if comm is None or not hasattr(comm, "all_reduce_add_rmsnorm"):
+            # TP=1 (no communicator) or a foreign communicator: local norm only
+            from .comm import fused_add_rms_norm_
+            x = allreduce_in if comm is None else comm.all_reduce(allreduce_in)
+            fused_add_rms_norm_(x, residual, weight, eps)
+            if x.data_ptr() != allreduce_in.data_ptr():
+                allreduce_in.copy_(x)
+            return
+        y, r = comm.all_reduce_add_rmsnorm(allreduce_in, residual, weight, eps, inplace=True)
+        if y.data_ptr() != allreduce_in.data_ptr():
+            allreduce_in.copy_(y)
+        if r is not None and r.data_ptr() != residual.data_ptr():
+            residual.copy_(r)
+
+    def fake(allreduce_in, residual, weight, eps, group_name) -> None:
+        return None
+
+    direct_register_custom_op(op_name="b200c_allreduce_add_rmsnorm", op_func=op,
+                              mutates_args=["allreduce_in", "residual"], fake_impl=fake)
+
+
+def _patch_platform() -> None:
+    from vllm.platforms import current_platform
+    cls = type(current_platform)
+    if getattr(cls, "_b200c_patched", False):
+        return
+    if not current_platform.is_cuda():
+        return  # CPU / other platforms keep their own communicator
+    cls.get_device_communicator_cls = classmethod(lambda c: COMM_QUALNAME)
+    cls._b200c_patched = True
+
+
+def register() -> None:
+    global _DONE
+    if _DONE or os.environ.get("B200C_DISABLE", "0") == "1":
+        return
+    _DONE = True
+    _patch_platform()
+    _register_fused_op()
+    if os.environ.get("B200C_FUSE_LAYERS", "1") == "1":
+        from . import model_patch
+        model_patch.apply()
+    if os.environ.get("B200C_PP_CHANNEL", "1") == "1":
+        from . import pp_channel
+        pp_channel.apply()
