@@ -70,6 +70,8 @@ def main():
     os.environ.setdefault("VLLM_WORKER_MULTIPROC_METHOD", "spawn")
     os.environ.setdefault("VLLM_LOGGING_LEVEL", "INFO")
     fi_aot = os.path.join(ROOT, "baseline", "_fi", "aot")
+    if os.path.isdir(fi_aot):
+        os.environ["B200C_FLASHINFER_AOT_DIR"] = fi_aot
 
     import random
     from vllm import LLM, SamplingParams

@@ -19,7 +19,7 @@ from vllm.logger import init_logger
 from . import _cabi as C
 from .comm import (DEFAULT_AG_BYTES, DEFAULT_MAX_BYTES, DEFAULT_P2P_BYTES, B200Comm)
 
-logger = init_logger(__name__)
+logger = init_logger("vllm.b200c.communicator")  # under vLLM's logging tree so INFO is shown
 
 
 def _group_kind(unique_name: str) -> str:

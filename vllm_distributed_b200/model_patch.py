@@ -77,6 +77,10 @@ def _configure_model(model) -> None:
         layer.self_attn.o_proj.reduce_results = False
         # the last layer of the stage hands a reduced tensor to the final norm / the PP send
         layer.mlp.down_proj.reduce_results = (i == len(layers) - 1)
+    from vllm.logger import init_logger
+    init_logger("vllm.b200c.model_patch").info(
+        "b200c: fused all-reduce+residual+RMSNorm on %d of %d decoder layers (group %s)",
+        sum(1 for l in layers if getattr(l, "_b200c_fused", False)), len(layers), tp.unique_name)
 
 
 def _wrap_model_init(model_cls) -> None:

@@ -61,11 +61,26 @@ def _patch_platform() -> None:
     cls._b200c_patched = True
 
 
+def _use_prebuilt_flashinfer() -> None:
+    """Benchmark convenience: let the stock FlashInfer comparator load a module that was
+    cross-compiled ahead of time (baseline/_fi/aot) instead of JIT-compiling for minutes."""
+    aot = os.environ.get("B200C_FLASHINFER_AOT_DIR")
+    if aot and os.path.isdir(aot):
+        import pathlib
+        from flashinfer.jit import env as jit_env
+        jit_env.FLASHINFER_AOT_DIR = pathlib.Path(aot)
+
+
 def register() -> None:
     global _DONE
-    if _DONE or os.environ.get("B200C_DISABLE", "0") == "1":
+    if _DONE:
+        return
+    _use_prebuilt_flashinfer()
+    if os.environ.get("B200C_DISABLE", "0") == "1":
         return
     _DONE = True
+    from vllm.logger import init_logger
+    init_logger("vllm.b200c.plugin").info("b200c plugin registered in pid %d", os.getpid())
     _patch_platform()
     _register_fused_op()
     if os.environ.get("B200C_FUSE_LAYERS", "1") == "1":
