@@ -1,0 +1,153 @@
+"""Host-side logic of the N>1 path on CPU: world_size 2 and 4 over gloo (no GPU, no compute calls
+into libb200c).  Covers the IPC-handle exchange, the PP tensor-dict channel (against the golden
+fixtures written by vLLM's own send/recv_tensor_dict) and bench.py's reference arm."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _spawn(fn, world, *args):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=fn, args=(r, world, port, q) + args) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    return dict(out)
+
+
+# ---- arena handle exchange ---------------------------------------------------------------------
+
+def _exchange_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from vllm_distributed_b200 import comm as bc
+    dist.init_process_group("gloo", rank=rank, world_size=world,
+                            init_method=f"tcp://127.0.0.1:{port}")
+    seen = {}
+    bc.arena_bytes = lambda w, a, b, c: 4096
+    bc.alloc_shared = lambda n: (1000 + rank, bytes([rank]) * 64)
+    bc.open_handle = lambda h: 2000 + h[0]
+
+    def fake_init(self, r, w, ptrs, max_bytes, ag_bytes, p2p_bytes, device, owned_arena=0, opened=None):
+        seen.update(rank=r, world=w, ptrs=list(ptrs), owned=owned_arena, opened=list(opened or []))
+        self.ctx = None
+        self._owned_arena = 0
+        self._opened = []
+    bc.B200Comm.__init__ = fake_init
+    bc.B200Comm.close = lambda self: None
+
+    class _NoDev:
+        def __enter__(self): return self
+        def __exit__(self, *a): return False
+    torch.cuda.device = lambda d: _NoDev()
+    bc.B200Comm.from_process_group(dist.group.WORLD, torch.device("cpu"), 1 << 20, 1 << 20, 1 << 20)
+    q.put((rank, seen))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_ipc_handle_exchange_orders_arenas_by_rank(world):
+    res = _spawn(_exchange_worker, world)
+    for rank, seen in res.items():
+        assert seen["rank"] == rank and seen["world"] == world
+        want = [1000 + r if r == rank else 2000 + r for r in range(world)]
+        assert seen["ptrs"] == want          # own arena at [rank], peers' mappings elsewhere
+        assert seen["owned"] == 1000 + rank
+        assert sorted(seen["opened"]) == sorted(p for p in want if p >= 2000)
+
+
+# ---- PP channel ------------------------------------------------------------------------------------
+
+class _FakeComm:
+    """Stands in for B200Communicator on a CPU box: CUDA tensors would go to send/recv."""
+    b200 = object()
+
+    def send(self, t, dst):
+        raise AssertionError("CPU tensors must not reach the device mailbox")
+
+    def recv(self, size, dtype, src):
+        raise AssertionError("CPU tensors must not reach the device mailbox")
+
+
+def _pp_worker(rank, world, port, q, tp, pp, golden):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    from oracle import oracle
+    from vllm.config import DeviceConfig, VllmConfig, set_current_vllm_config
+    from vllm.distributed import parallel_state as ps
+    from vllm_distributed_b200 import pp_channel
+    g = dict(np.load(golden))
+    got = {}
+    with set_current_vllm_config(VllmConfig(device_config=DeviceConfig(device="cpu"))):
+        ps.init_distributed_environment(world_size=world, rank=rank, local_rank=rank,
+                                        distributed_init_method=f"tcp://127.0.0.1:{port}",
+                                        backend="gloo")
+        ps.initialize_model_parallel(tp, pp)
+        pp_channel.apply()
+        ppg = ps.get_pp_group()
+        ppg.device_communicator = _FakeComm()   # route through the patched channel
+        tpg = ps.get_tp_group() if tp > 1 else None
+        hs, rs = oracle.from_bits(g["hidden_states_in"]), oracle.from_bits(g["residual_in"])
+        for step in range(3):  # several steps: the channel must stay in lock-step
+            if ppg.rank_in_group == 0:
+                ppg.send_tensor_dict({"hidden_states": hs, "residual": rs, "step": step},
+                                     all_gather_group=tpg)
+            else:
+                d = ppg.recv_tensor_dict(all_gather_group=tpg)
+                assert d["step"] == step
+                got = {k: oracle.to_bits(v) for k, v in d.items() if isinstance(v, torch.Tensor)}
+        torch.distributed.barrier()
+    q.put((rank, (ppg.rank_in_group, ps.get_tp_group().rank_in_group, got)))
+    ps.destroy_model_parallel()
+    ps.destroy_distributed_environment()
+
+
+@pytest.mark.parametrize("name,tp,pp", [("pp2_tp1", 1, 2), ("pp2_tp2", 2, 2)])
+def test_pp_channel_matches_vllm_golden(golden_dir, name, tp, pp):
+    golden = os.path.join(golden_dir, name + ".npz")
+    g = dict(np.load(golden))
+    res = _spawn(_pp_worker, tp * pp, tp, pp, golden)
+    receivers = 0
+    for rank, (pp_rank, tp_rank, got) in res.items():
+        if pp_rank == 1:
+            receivers += 1
+            assert np.array_equal(got["hidden_states"], g[f"hidden_states_out_tp{tp_rank}"])
+            assert np.array_equal(got["residual"], g[f"residual_out_tp{tp_rank}"])
+    assert receivers == tp
+
+
+# ---- bench.py reference arm ------------------------------------------------------------------------
+
+def test_bench_reference_arm_prints_contract_line():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                          "--gpus", "2", "--steps", "1", "--warmup", "1", "--batch", "2"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    r = json.loads(lines[0])
+    assert r["impl"] == "reference" and r["n_gpus"] == 2 and r["value"] > 0
+    assert r["cpu_baseline"]["kind"] in ("reference", "port") and r["cpu_baseline"]["cores"] >= 1
+    assert r["e2e"]["h2d_bytes_per_step"] == 0 and r["e2e"]["d2h_bytes_per_step"] == 0
+    for k in ("metric", "unit", "steps", "warmup", "ms_per_step", "higher_is_better", "config"):
+        assert k in r
