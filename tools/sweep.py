@@ -211,7 +211,7 @@ def main():
                 except Exception as e:  # noqa: BLE001
                     row["vllm_ca_error"] = f"{type(e).__name__}: {e}"[:200]
 
-            if fi is not None and T > n:  # two-shot asserts token_num > world_size
+            if fi is not None:
                 ficomm, ws = fi
                 try:
                     ro, no = torch.empty_like(res), torch.empty_like(res)
@@ -222,7 +222,7 @@ def main():
                             pattern=ficomm.AllReduceFusionPattern.kARResidualRMSNorm,
                             launch_with_pdl=True, trigger_completion_at_end=T > 16,
                             residual_out=ro, norm_out=no, residual_in=res, rms_gamma=gamma,
-                            rms_eps=1e-5, use_oneshot=oneshot, fp32_acc=True)
+                            rms_eps=1e-5, use_oneshot=(True if T <= n else oneshot), fp32_acc=True)
                     row["flashinfer_auto_us"] = round(time_graph(fi_call, iters, 3, dev, n), 2)
                 except Exception as e:  # noqa: BLE001
                     row["flashinfer_error"] = f"{type(e).__name__}: {e}"[:200]

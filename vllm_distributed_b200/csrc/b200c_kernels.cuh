@@ -194,37 +194,71 @@ __device__ __forceinline__ void push_range(const char* in, char* dst, size_t lo,
   }
 }
 
-// Two-shot scatter: for each offset inside a chunk, the N-1 vectors bound for the N-1 peers
-// are loaded together and pushed together, so every peer link is fed at the same time and a
-// small message costs one load round trip instead of one per peer.  Slot k is the k-th peer to
-// the right of this rank.
-__device__ __forceinline__ void scatter_chunks(const RankParams& p, uint32_t b, size_t chunk,
-                                               size_t nvec, size_t tid, size_t nthreads) {
+// Two-shot scatter: for each offset inside a chunk, the vectors bound for the NP peers are loaded
+// together and pushed together, so every peer link is fed at the same time and a small message
+// costs one load round trip instead of one per peer.  UO offsets are handled per trip so that a
+// thread keeps UO*NP independent 16-byte loads in flight whatever the group size (2 ranks: 8x1,
+// <=4 ranks: 3x3, else 1x7).  Slot k is the k-th peer to the right of this rank.
+template <int UO, int NP>
+__device__ __forceinline__ void scatter_chunks_t(const RankParams& p, uint32_t b, size_t chunk,
+                                                 size_t nvec, size_t tid, size_t nthreads) {
   const size_t slot = (size_t)p.rank * chunk * 16;
-  for (size_t off = tid; off < chunk; off += nthreads) {
-    uint4 v[kMaxRanks - 1];
+  for (size_t base = tid; base < chunk; base += nthreads * UO) {
+    uint4 v[UO][NP];
 #pragma unroll
-    for (int k = 0; k < kMaxRanks - 1; ++k) {
-      if (k + 1 < p.world) {
-        int owner = p.rank + k + 1;
-        owner = owner >= p.world ? owner - p.world : owner;
-        const size_t idx = (size_t)owner * chunk + off;
-        if (idx < nvec) v[k] = ld_stream_v4((const char*)p.in + idx * 16);
+    for (int u = 0; u < UO; ++u) {
+      const size_t off = base + (size_t)u * nthreads;
+#pragma unroll
+      for (int k = 0; k < NP; ++k) {
+        if (k + 1 < p.world && off < chunk) {
+          int owner = p.rank + k + 1;
+          owner = owner >= p.world ? owner - p.world : owner;
+          const size_t idx = (size_t)owner * chunk + off;
+          if (idx < nvec) v[u][k] = ld_stream_v4((const char*)p.in + idx * 16);
+        }
       }
     }
 #pragma unroll
-    for (int k = 0; k < kMaxRanks - 1; ++k) {
-      if (k + 1 < p.world) {
-        int owner = p.rank + k + 1;
-        owner = owner >= p.world ? owner - p.world : owner;
-        const size_t idx = (size_t)owner * chunk + off;
-        if (idx < nvec) {
-          scrub(v[k]);
-          st_push_v4(lam_region(p, owner, b) + slot + off * 16, v[k]);
+    for (int u = 0; u < UO; ++u) {
+      const size_t off = base + (size_t)u * nthreads;
+#pragma unroll
+      for (int k = 0; k < NP; ++k) {
+        if (k + 1 < p.world && off < chunk) {
+          int owner = p.rank + k + 1;
+          owner = owner >= p.world ? owner - p.world : owner;
+          const size_t idx = (size_t)owner * chunk + off;
+          if (idx < nvec) {
+            scrub(v[u][k]);
+            st_push_v4(lam_region(p, owner, b) + slot + off * 16, v[u][k]);
+          }
         }
       }
     }
   }
+}
+
+__device__ __forceinline__ void scatter_chunks(const RankParams& p, uint32_t b, size_t chunk,
+                                               size_t nvec, size_t tid, size_t nthreads) {
+  if (nvec > (size_t)(8u << 20) / 16 && p.world > 2) {
+    // above 8 MiB (measured on 8 x B200) streaming one contiguous range per peer, peer after
+    // peer starting at the right-hand neighbour, beats seven interleaved streams
+    for (int k = 1; k < p.world; ++k) {
+      int owner = p.rank + k;
+      owner = owner >= p.world ? owner - p.world : owner;
+      const size_t lo = (size_t)owner * chunk;
+      const size_t hi = (lo + chunk < nvec) ? lo + chunk : nvec;
+      if (lo < hi)
+        push_range<4>((const char*)p.in, lam_region(p, owner, b) + (size_t)p.rank * chunk * 16, lo,
+                      hi, tid, nthreads);
+    }
+    return;
+  }
+  if (p.world == 2)
+    scatter_chunks_t<8, 1>(p, b, chunk, nvec, tid, nthreads);
+  else if (p.world <= 4)
+    scatter_chunks_t<3, 3>(p, b, chunk, nvec, tid, nthreads);
+  else
+    scatter_chunks_t<1, 7>(p, b, chunk, nvec, tid, nthreads);
 }
 
 // ---- two-shot phase B: reduce my chunk, push the rounded sums into every rank's hi half -----------
