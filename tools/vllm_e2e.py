@@ -51,7 +51,7 @@ def main():
     ap.add_argument("--pp", type=int, default=1)
     ap.add_argument("--model-shape", default="llama3-8b", choices=sorted(SHAPES))
     ap.add_argument("--layers", type=int, default=0)
-    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--batch", type=int, nargs="+", default=[64])
     ap.add_argument("--prompt-len", type=int, default=1024)
     ap.add_argument("--decode", type=int, default=128)
     ap.add_argument("--plugin", default="on", choices=["on", "off"])
@@ -84,37 +84,40 @@ def main():
     llm = LLM(model=model_dir, tensor_parallel_size=args.tp, pipeline_parallel_size=args.pp,
               load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", seed=0,
               max_model_len=args.prompt_len + args.decode + 16, gpu_memory_utilization=0.85,
-              enforce_eager=args.eager, max_num_seqs=max(args.batch, 8),
+              enforce_eager=args.eager, max_num_seqs=max(max(args.batch), 8),
               max_num_batched_tokens=max(8192, args.prompt_len),
               distributed_executor_backend="mp" if args.tp * args.pp > 1 else None,
               compilation_config=comp or None, enable_prefix_caching=False)
     t_init = time.time() - t0
-    rng = random.Random(1234)
     vocab = SHAPES[args.model_shape]["vocab_size"]
-    prompts = [{"prompt_token_ids": [rng.randrange(1000, vocab - 1000) for _ in range(args.prompt_len)]}
-               for _ in range(args.batch)]
+    all_tokens = {}
+    for batch in args.batch:
+        rng = random.Random(1234)
+        prompts = [{"prompt_token_ids": [rng.randrange(1000, vocab - 1000) for _ in range(args.prompt_len)]}
+                   for _ in range(batch)]
 
-    def run(max_tokens):
-        sp = SamplingParams(temperature=0.0, max_tokens=max_tokens, ignore_eos=True, detokenize=False)
-        t = time.time()
-        outs = llm.generate(prompts, sp, use_tqdm=False)
-        return time.time() - t, [list(o.outputs[0].token_ids) for o in outs]
+        def run(max_tokens):
+            sp = SamplingParams(temperature=0.0, max_tokens=max_tokens, ignore_eos=True, detokenize=False)
+            t = time.time()
+            outs = llm.generate(prompts, sp, use_tqdm=False)
+            return time.time() - t, [list(o.outputs[0].token_ids) for o in outs]
 
-    run(4)  # warm-up (graph replay paths, allocator)
-    t_prefill, _ = run(1)
-    t_full, toks = run(args.decode)
-    t_decode = max(1e-9, t_full - t_prefill)
-    digest = hashlib.sha256(json.dumps(toks).encode()).hexdigest()[:16]
-    res = {"tp": args.tp, "pp": args.pp, "shape": args.model_shape, "layers": args.layers or
-           SHAPES[args.model_shape]["num_hidden_layers"], "batch": args.batch,
-           "prompt_len": args.prompt_len, "decode": args.decode, "plugin": args.plugin,
-           "fuse_layers": args.fuse_layers, "eager": args.eager,
-           "decode_tokens_per_s": round(args.batch * (args.decode - 1) / t_decode, 1),
-           "prefill_s": round(t_prefill, 4), "full_s": round(t_full, 4),
-           "init_s": round(t_init, 1), "digest": digest}
-    print("E2E_RESULT " + json.dumps(res), flush=True)
+        run(4)  # warm-up (graph replay paths, allocator)
+        t_prefill, _ = run(1)
+        t_full, toks = run(args.decode)
+        t_decode = max(1e-9, t_full - t_prefill)
+        digest = hashlib.sha256(json.dumps(toks).encode()).hexdigest()[:16]
+        res = {"tp": args.tp, "pp": args.pp, "shape": args.model_shape, "layers": args.layers or
+               SHAPES[args.model_shape]["num_hidden_layers"], "batch": batch,
+               "prompt_len": args.prompt_len, "decode": args.decode, "plugin": args.plugin,
+               "stock_fusion": args.stock_fusion, "fuse_layers": args.fuse_layers, "eager": args.eager,
+               "decode_tokens_per_s": round(batch * (args.decode - 1) / t_decode, 1),
+               "prefill_s": round(t_prefill, 4), "full_s": round(t_full, 4),
+               "init_s": round(t_init, 1), "digest": digest}
+        print("E2E_RESULT " + json.dumps(res), flush=True)
+        all_tokens[str(batch)] = {"result": res, "tokens": toks}
     if args.out:
-        json.dump({"result": res, "tokens": toks}, open(args.out, "w"))
+        json.dump(all_tokens, open(args.out, "w"))
     del llm
 
 
