@@ -1,0 +1,129 @@
+"""Compatibility shim: lets the reference launcher's bring-up run on the installed vLLM (0.22).
+
+The reference (`launch.py` / `rpc.py` / `rpc_reader.py` of koush/vllm-distributed) targets a
+vLLM ~0.10 whose import paths have since moved.  This module does not
+contain or modify the launcher: it installs the moved names under their old import paths and
+adapts the two signatures that changed, then runs the launcher file the user points it at:
+
+    python -m vllm_distributed_b200.launch_shim /path/to/vllm-distributed/src/launch.py serve ...
+
+What is mapped (old name used by launch.py -> where it lives in vLLM 0.22):
+  vllm.utils.FlexibleArgumentParser              -> vllm.utils.argparse_utils
+  vllm.utils.get_ip / get_open_port / get_distributed_init_method -> vllm.utils.network_utils
+  vllm.utils.run_method                          -> vllm.v1.serial_utils
+  vllm.utils.cuda_device_count_stateless         -> torch / vllm.platforms.cuda
+  vllm.worker.worker_base.WorkerWrapperBase      -> vllm.v1.worker.worker_base (ctor adapter)
+  vllm.entrypoints.openai.tool_parsers.ToolParserManager -> vllm.tool_parsers
+  vllm.entrypoints.openai.api_server.load_log_config -> ...openai.server_utils
+  vllm.entrypoints.openai.api_server.maybe_register_tokenizer_info_endpoint -> removed (no-op)
+It also registers the b200c plugin in the launcher process, so every worker it spawns (local
+fork or remote node) selects B200Communicator.
+"""
+from __future__ import annotations
+
+import importlib
+import os
+import runpy
+import sys
+import types
+
+
+def _ensure_module(name: str) -> types.ModuleType:
+    try:
+        return importlib.import_module(name)
+    except Exception:
+        mod = types.ModuleType(name)
+        sys.modules[name] = mod
+        parent, _, child = name.rpartition(".")
+        if parent:
+            setattr(_ensure_module(parent), child, mod)
+        return mod
+
+
+def _first_attr(candidates):
+    """candidates: iterable of (module, attr); returns the first that imports."""
+    for mod, attr in candidates:
+        try:
+            return getattr(importlib.import_module(mod), attr)
+        except Exception:
+            continue
+    return None
+
+
+def install() -> dict[str, str]:
+    """Install the aliases; returns {old dotted name: 'mapped' | 'stub' | 'present'}."""
+    report: dict[str, str] = {}
+
+    def alias(old_mod: str, name: str, candidates, stub=None):
+        mod = _ensure_module(old_mod)
+        key = f"{old_mod}.{name}"
+        if hasattr(mod, name):
+            report[key] = "present"
+            return
+        obj = _first_attr(candidates)
+        if obj is None:
+            obj, report[key] = stub, "stub"
+        else:
+            report[key] = "mapped"
+        setattr(mod, name, obj)
+
+    alias("vllm.utils", "FlexibleArgumentParser",
+          [("vllm.utils.argparse_utils", "FlexibleArgumentParser")])
+    for fn in ("get_ip", "get_open_port", "get_distributed_init_method"):
+        alias("vllm.utils", fn, [("vllm.utils.network_utils", fn)])
+    alias("vllm.utils", "run_method", [("vllm.v1.serial_utils", "run_method"),
+                                       ("vllm.utils.func_utils", "run_method")])
+
+    def _device_count() -> int:
+        import torch
+        return torch.cuda.device_count() if torch.cuda.is_available() else 0
+    alias("vllm.utils", "cuda_device_count_stateless",
+          [("vllm.utils.torch_utils", "cuda_device_count_stateless")], stub=_device_count)
+
+    alias("vllm.entrypoints.openai.tool_parsers", "ToolParserManager",
+          [("vllm.tool_parsers", "ToolParserManager"),
+           ("vllm.tool_parsers.abstract_tool_parser", "ToolParserManager")])
+    alias("vllm.entrypoints.openai.api_server", "load_log_config",
+          [("vllm.entrypoints.openai.server_utils", "load_log_config")],
+          stub=lambda *_a, **_k: None)
+    alias("vllm.entrypoints.openai.api_server", "maybe_register_tokenizer_info_endpoint",
+          [], stub=lambda *_a, **_k: None)
+
+    # WorkerWrapperBase: the launcher calls WorkerWrapperBase.__init__(vllm_config, rpc_rank);
+    # 0.22's constructor is (rpc_rank, global_rank=None).
+    wb = _ensure_module("vllm.worker.worker_base")
+    _ensure_module("vllm.worker")
+    if not hasattr(wb, "WorkerWrapperBase"):
+        new_base = _first_attr([("vllm.v1.worker.worker_base", "WorkerWrapperBase")])
+        if new_base is not None:
+            class WorkerWrapperBase(new_base):  # type: ignore[misc, valid-type]
+                def __init__(self, vllm_config, rpc_rank: int = 0, *args, **kwargs):
+                    try:
+                        super().__init__(rpc_rank, *args, **kwargs)
+                    except TypeError:
+                        super().__init__(vllm_config, rpc_rank, *args, **kwargs)
+                    self.vllm_config = vllm_config
+            wb.WorkerWrapperBase = WorkerWrapperBase
+            report["vllm.worker.worker_base.WorkerWrapperBase"] = "mapped"
+        else:
+            report["vllm.worker.worker_base.WorkerWrapperBase"] = "stub"
+    else:
+        report["vllm.worker.worker_base.WorkerWrapperBase"] = "present"
+    return report
+
+
+def main(argv: list[str] | None = None) -> None:
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if not argv:
+        raise SystemExit("usage: python -m vllm_distributed_b200.launch_shim <launch.py> [args...]")
+    script = os.path.abspath(argv[0])
+    install()
+    from . import plugin
+    plugin.register()
+    sys.path.insert(0, os.path.dirname(script))  # launch.py imports its siblings rpc / rpc_reader
+    sys.argv = [script] + argv[1:]
+    runpy.run_path(script, run_name="__main__")
+
+
+if __name__ == "__main__":
+    main()
