@@ -26,6 +26,23 @@ def _group_kind(unique_name: str) -> str:
     return unique_name.split(":")[0]
 
 
+class StreamHandle:
+    """vLLM's Handle protocol (parallel_state.py:73-78) over a CUDA stream: wait() makes the
+    current stream wait for everything enqueued so far on the side stream -- no host block."""
+
+    def __init__(self, stream: "torch.cuda.Stream", wait_needed: bool):
+        self.event = torch.cuda.Event()
+        self.event.record(stream)
+        self.wait_needed = wait_needed
+
+    def is_completed(self) -> bool:
+        return self.event.query()
+
+    def wait(self) -> None:
+        if self.wait_needed:
+            torch.cuda.current_stream().wait_event(self.event)
+
+
 class B200Communicator(CudaCommunicator):
     def __init__(self, cpu_group, device=None, device_group=None, unique_name: str = "", **kw):
         super().__init__(cpu_group, device, device_group, unique_name, **kw)
@@ -115,6 +132,33 @@ class B200Communicator(CudaCommunicator):
             if b.can_p2p(tensor):
                 return b.recv(tensor, src)
         return super().recv(size, dtype, src)
+
+    # ---- asynchronous flavour used by the tensor-dict channel (pp_channel.py) -----------------
+    # NCCL's isend/irecv run on NCCL's own stream, so the compute stream keeps preparing the
+    # next step while a hop is in flight.  Same here: sends and receives are enqueued on two
+    # side streams, ordered against the compute stream with events only.
+    def _side_streams(self):
+        if getattr(self, "_send_stream", None) is None:
+            self._send_stream = torch.cuda.Stream(device=self.device)
+            self._recv_stream = torch.cuda.Stream(device=self.device)
+        return self._send_stream, self._recv_stream
+
+    def isend(self, tensor: torch.Tensor, dst: int) -> "StreamHandle":
+        send_stream, _ = self._side_streams()
+        send_stream.wait_stream(torch.cuda.current_stream(self.device))  # tensor is produced first
+        with torch.cuda.stream(send_stream):
+            self.b200.send(tensor, dst)
+        tensor.record_stream(send_stream)
+        return StreamHandle(send_stream, wait_needed=False)
+
+    def irecv(self, size: torch.Size, dtype: torch.dtype, src: int):
+        _, recv_stream = self._side_streams()
+        tensor = torch.empty(size, dtype=dtype, device=self.device)
+        recv_stream.wait_stream(torch.cuda.current_stream(self.device))  # allocation is ordered first
+        with torch.cuda.stream(recv_stream):
+            self.b200.recv(tensor, src)
+        tensor.record_stream(recv_stream)
+        return tensor, StreamHandle(recv_stream, wait_needed=True)
 
     def destroy(self):
         if self.b200 is not None:

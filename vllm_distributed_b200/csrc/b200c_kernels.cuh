@@ -30,8 +30,8 @@ struct LocalState {
   uint32_t ag_seq;       // all-gather call counter
   uint32_t ag_arrive_push;
   uint32_t ag_arrive_done;
-  uint32_t p2p_arrive;
-  uint32_t pad0;
+  uint32_t p2p_arrive_send;  // send and recv kernels of one ctx may run on different streams
+  uint32_t p2p_arrive_recv;
   unsigned long long dirty_lo[3];  // bytes peers wrote into each region's lo / hi half
   unsigned long long dirty_hi[3];
   uint32_t send_seq[kMaxRanks];
@@ -868,9 +868,9 @@ __device__ __forceinline__ void send_body(const CopyParams& p) {
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
-    const uint32_t prev = atomicAdd(&p.st->p2p_arrive, 1u);
+    const uint32_t prev = atomicAdd(&p.st->p2p_arrive_send, 1u);
     if (prev == gridDim.x - 1) {
-      p.st->p2p_arrive = 0;
+      p.st->p2p_arrive_send = 0;
       __threadfence_system();
       st_release_sys(ctrl_flag(p.arena[p.peer], kP2pReadyOff, p.rank * 2 + (int)slot), m + 1);
       p.st->send_seq[p.peer] = m + 1;
@@ -891,9 +891,9 @@ __device__ __forceinline__ void recv_body(const CopyParams& p) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
-    const uint32_t prev = atomicAdd(&p.st->p2p_arrive, 1u);
+    const uint32_t prev = atomicAdd(&p.st->p2p_arrive_recv, 1u);
     if (prev == gridDim.x - 1) {
-      p.st->p2p_arrive = 0;
+      p.st->p2p_arrive_recv = 0;
       __threadfence_system();
       st_release_sys(ctrl_flag(p.arena[p.peer], kP2pCreditOff, p.rank * 2 + (int)slot), m + 1);
       p.st->recv_seq[p.peer] = m + 1;

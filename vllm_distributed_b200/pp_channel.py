@@ -57,7 +57,11 @@ def isend_tensor_dict(self, tensor_dict, dst=None, all_gather_group=None, all_ga
         if _use_slices(self, key, t.numel(), all_gather_group, all_gather_tensors):
             t = t.reshape(ag_size, -1)[ag_rank]
         if t.is_cuda:
-            comm.send(t.contiguous(), dst)  # stream-ordered; nothing to wait for on the host
+            tc = t.contiguous()
+            if hasattr(comm, "isend") and comm.b200.can_p2p(tc):
+                handles.append(comm.isend(tc, dst))  # side stream; never blocks the host
+            else:
+                comm.send(tc, dst)
         else:
             handles.append(torch.distributed.isend(t, dst=self.ranks[dst], group=self.cpu_group))
     return handles
@@ -89,6 +93,9 @@ def irecv_tensor_dict(self, src=None, all_gather_group=None, all_gather_tensors=
         if value.device == "cpu":
             t = torch.empty(shape, dtype=value.dtype, device="cpu")
             handles.append(torch.distributed.irecv(t, src=self.ranks[src], group=self.cpu_group))
+        elif hasattr(comm, "irecv"):
+            t, h = comm.irecv(shape, value.dtype, src)
+            handles.append(h)
         else:
             t = comm.recv(shape, value.dtype, src)
         out[key] = t
