@@ -361,6 +361,23 @@ def test_error_codes(pkg):
     g.check_health()
 
 
+def test_auto_falls_back_to_two_shot_when_one_shot_does_not_fit(pkg):
+    """An arena sized exactly for the message (as bench.py builds it) cannot hold `world` copies:
+    AUTO must then take the two-shot path instead of failing."""
+    g = group(pkg, 4, max_bytes=64 * 1024, ag_bytes=1 << 20, p2p_bytes=1 << 20)
+    xs = [rand((4, 8192), torch.bfloat16, 900 + r) for r in range(4)]   # 64 KiB per rank
+    ref = oracle.all_reduce(xs)
+    for o in g.all_reduce([x.cuda() for x in xs], variant=0):
+        assert bits_equal(o, ref)
+    res, gamma = rand((4, 8192), torch.bfloat16, 7), rand((8192,), torch.bfloat16, 8)
+    y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+    ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs], [res.cuda() for _ in range(4)],
+                                      gamma.cuda(), 1e-5, variant=0)
+    assert bits_equal(rs[0], r_ref)
+    check_norm(ys[0], y_ref, torch.bfloat16)
+    g.check_health()
+
+
 def test_full_size_properties(pkg):
     """BASELINE sweep maximum (8192 tokens x 8192 hidden, bf16 = 128 MiB): too slow for the CPU
     oracle in a unit test, so check size-independent properties instead."""

@@ -209,7 +209,9 @@ void norm_shape(int hv, int* vpt, int* threads) {
 
 int pick_variant(const b200c_ctx* c, size_t bytes, int variant) {
   if (variant == B200C_ONESHOT || variant == B200C_TWOSHOT) return variant;
-  return ((long long)bytes <= c->oneshot_max_bytes) ? B200C_ONESHOT : B200C_TWOSHOT;
+  // AUTO: one-shot below the measured crossover, provided `world` copies fit one region
+  const bool fits = bytes * (size_t)c->world <= c->geom.lam_stride;
+  return ((long long)bytes <= c->oneshot_max_bytes && fits) ? B200C_ONESHOT : B200C_TWOSHOT;
 }
 
 int check_ar_fit(const b200c_ctx* c, size_t bytes, int variant) {
@@ -578,7 +580,7 @@ int b200c_init(int rank, int world, void* const* arena_ptrs, size_t max_bytes, s
   c->twoshot_blocks = c->sm_count;
   // one-shot / two-shot crossover measured on 8 x B200 (tools/sweep.py, profiles/): the more
   // ranks, the sooner (N-1)*S of one-shot link traffic costs more than a second fabric hop
-  c->oneshot_max_bytes = world <= 2 ? (2 << 20) : world <= 4 ? (1 << 20) : (384 << 10);
+  c->oneshot_max_bytes = world <= 2 ? (2 << 20) : world <= 4 ? (512 << 10) : (384 << 10);
   if (world > 1) {
     c->max_bytes = max_bytes;
     c->ag_bytes = ag_bytes;
