@@ -464,7 +464,17 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vllm", action="store_true", help="reference arm: skip vLLM, time the port")
     args = ap.parse_args()
-    res = run_reference(args) if args.impl == "reference" else run_ours(args)
+    # Libraries (NCCL's version banner, vLLM's logger) write to stdout; the contract is ONE JSON
+    # line there.  Everything else is sent to stderr while the run is in progress.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        res = run_reference(args) if args.impl == "reference" else run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if res is not None:
         print(json.dumps(res), flush=True)
 
