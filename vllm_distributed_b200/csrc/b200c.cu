@@ -193,8 +193,16 @@ int coresident_clusters(K kernel, int threads, int cluster, int sm_count, int* o
 // two-shot role split: CTAs [0, link) push over the link, the rest run the rows
 int link_split(const b200c_ctx* c, int grid) {
   if (grid < 2) return 0;
-  int l = c->link_blocks > 0 ? c->link_blocks : grid / 2;
+  // measured (tools/sweep.py): ~32 link CTAs feed the fabric for a 148-CTA grid, 64 for 296;
+  // every further CTA is worth more on the row (HBM) side
+  int l = c->link_blocks > 0 ? c->link_blocks : std::min(64, std::max(1, grid / 4));
   return std::max(1, std::min(l, grid - 1));
+}
+
+// two-shot grid: one CTA per SM below 2 MiB (launch + scheduling cost dominates), the full
+// two-per-SM residency above
+int twoshot_grid(const b200c_ctx* c, size_t bytes) {
+  return bytes >= (size_t)(2u << 20) ? c->twoshot_blocks : std::min(c->twoshot_blocks, c->sm_count);
 }
 
 // rows are split over `threads` lanes holding up to VPT vectors each
@@ -430,7 +438,7 @@ int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
       }
     }
   }
-  const int want = two ? c0->twoshot_blocks : std::min(tokens, c0->oneshot_blocks);
+  const int want = two ? twoshot_grid(c0, bytes) : std::min(tokens, c0->oneshot_blocks);
   switch (dtype) {
     case B200C_BF16: return launch_ar_norm_v<__nv_bfloat16>(ctxs, nemu, rp, vpt, threads, two, want, s);
     case B200C_F16: return launch_ar_norm_v<__half>(ctxs, nemu, rp, vpt, threads, two, want, s);
@@ -467,7 +475,7 @@ int ar_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins, void* cons
   if (rc) return rc;
   const bool two = variant == B200C_TWOSHOT;
   const size_t nvec = bytes / 16;
-  int want = two ? c0->twoshot_blocks : c0->oneshot_blocks;
+  int want = two ? twoshot_grid(c0, bytes) : c0->oneshot_blocks;
   want = (int)std::min<size_t>((size_t)want, (nvec + 511) / 512);
   if (two) want = std::max(want, 2);
 #define B200C_AR(T) \
@@ -577,7 +585,7 @@ int b200c_init(int rank, int world, void* const* arena_ptrs, size_t max_bytes, s
     return rc;
   }
   c->oneshot_blocks = c->sm_count;
-  c->twoshot_blocks = c->sm_count;
+  c->twoshot_blocks = 2 * c->sm_count;  // two resident CTAs per SM (clamped to what fits)
   // one-shot / two-shot crossover measured on 8 x B200 (tools/sweep.py, profiles/): the more
   // ranks, the sooner (N-1)*S of one-shot link traffic costs more than a second fabric hop
   c->oneshot_max_bytes = world <= 2 ? (2 << 20) : world <= 4 ? (512 << 10) : (384 << 10);

@@ -4,6 +4,11 @@
 
 #include "b200c_device.cuh"
 
+// Resident CTAs per SM the two-shot kernels are compiled for (register cap = 65536 / 512 / this).
+#ifndef B200C_TWOSHOT_CTAS_PER_SM
+#define B200C_TWOSHOT_CTAS_PER_SM 2  // measured: the kernels are bound by bytes in flight per SM
+#endif
+
 namespace b200c {
 
 // ---- arena layout (bytes from the arena base; identical on every rank) -----------------------
@@ -137,26 +142,29 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
   for (size_t i = gtid; i < n; i += gsize) st_v4(base + i * 16, m);
 }
 
-// Call bookkeeping without an end-of-kernel rendezvous and without a fence: the epoch and the
-// tickets of the running call share one 64-bit word, so thread 0 of every CTA learns the epoch
-// and takes its ticket with ONE atomic.  The CTA holding the last ticket knows that every CTA of
-// this rank has already read the epoch and may publish (epoch+1, 0 tickets) and the extents
-// this call dirties whenever it likes -- the next kernel is the only reader.
+// Call bookkeeping without an end-of-kernel rendezvous and without a fence: the epoch (high
+// half) and the tickets of the running call (low half) share one 64-bit word.  A CTA reads the
+// epoch, and only when all its threads have it does thread 0 take a ticket.  The CTA holding the
+// last ticket therefore knows that every CTA of this rank has already read the epoch and may
+// publish (epoch+1, 0 tickets) and the extents this call dirties whenever it likes -- the next
+// kernel is the only reader.
 struct CallState {
   uint32_t epoch;
   uint32_t ticket;  // meaningful in thread 0 only
 };
 
-__device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* s_epoch) {
+__device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* /*unused*/) {
+  // Every thread reads the epoch itself (one L2 hit, no shared-memory broadcast) and consumes
+  // the value before the barrier, so when thread 0 takes the CTA's ticket afterwards every
+  // thread of the CTA has finished reading it.  The ticket's own latency is off the critical
+  // path: its value is needed only in end_call.
   CallState cs;
   cs.ticket = 0;
-  if (threadIdx.x == 0) {
-    const unsigned long long w = atomicAdd(&p.st->call, 1ull);
-    cs.ticket = (uint32_t)w;
-    *s_epoch = (uint32_t)(w >> 32);
-  }
+  const uint32_t* hi = reinterpret_cast<const uint32_t*>(&p.st->call) + 1;  // little endian
+  cs.epoch = ld_volatile_u32(hi);
+  if (cs.epoch == 0xffffffffu) __trap();  // forces the load to have returned here
   __syncthreads();
-  cs.epoch = *s_epoch;
+  if (threadIdx.x == 0) cs.ticket = (uint32_t)atomicAdd(&p.st->call, 1ull);
   return cs;
 }
 
@@ -705,24 +713,24 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
 // ---- kernels: a real launch carries one rank, an emulated launch carries all of them ----------
 
 template <typename T, int VPT, bool TWOSHOT>
-__global__ void __launch_bounds__(512) ar_norm_kernel(const __grid_constant__ RankParams p) {
+__global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_norm_kernel(const __grid_constant__ RankParams p) {
   __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
   ar_norm_body<T, VPT, TWOSHOT>(p, smem);
 }
 
 template <typename T, int VPT, bool TWOSHOT>
-__global__ void __launch_bounds__(512) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
+__global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
   __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
   ar_norm_body<T, VPT, TWOSHOT>(ep.r[blockIdx.y], smem);
 }
 
 template <typename T, bool TWOSHOT>
-__global__ void __launch_bounds__(512) ar_kernel(const __grid_constant__ RankParams p) {
+__global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_kernel(const __grid_constant__ RankParams p) {
   ar_body<T, TWOSHOT>(p);
 }
 
 template <typename T, bool TWOSHOT>
-__global__ void __launch_bounds__(512) ar_kernel_emu(const __grid_constant__ EmuParams ep) {
+__global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_kernel_emu(const __grid_constant__ EmuParams ep) {
   ar_body<T, TWOSHOT>(ep.r[blockIdx.y]);
 }
 
