@@ -155,7 +155,9 @@ int b200c_rms_norm(void* out, const void* x, const void* gamma, float eps, int t
                    int dtype, void* stream);
 
 /* lm_head logits gather: out[row, r*cols + c] = in_r[row, c]   (bit-exact byte move).
- * row_bytes = bytes of one rank's row (cols * sizeof(T)), multiple of 16.
+ * row_bytes = bytes of one rank's row (cols * sizeof(T)), a multiple of 4: 16-byte vectors when
+ * it allows, 8- or 4-byte words otherwise (the [batch, 2] fp32 pairs of vLLM's vocab-parallel
+ * argmax, VLLM/model_executor/layers/logits_processor.py:106-156, travel this way).
  * Replaces tensor_model_parallel_all_gather(dim=-1)
  * (VLLM/distributed/device_communicators/base_device_communicator.py:184-207,
  * called from VLLM/model_executor/layers/logits_processor.py:75-87). */

@@ -271,6 +271,34 @@ def test_all_gather_bit_exact(pkg, world):
     g.check_health()
 
 
+@pytest.mark.parametrize("world", [2, 8])
+def test_all_gather_narrow_rows_and_vocab_parallel_argmax(pkg, world):
+    """Rows of 8 and 4 bytes (not a multiple of 16), and vLLM's vocab-parallel argmax built on
+    them (logits_processor.py:106-156): gather [batch, 2] fp32 (value, global index) pairs."""
+    g = group(pkg, world)
+    gen = torch.Generator().manual_seed(77)
+    for rows, cols, dtype in [(5, 2, torch.float32), (64, 1, torch.float32), (3, 6, torch.bfloat16),
+                              (256, 2, torch.float32)]:
+        slabs = [torch.randn(rows, cols, generator=gen).to(dtype) for _ in range(world)]
+        ref = oracle.all_gather_lastdim(slabs)
+        outs = g.all_gather_lastdim([s.cuda() for s in slabs])
+        for o in outs:
+            assert bits_equal(o, ref), (rows, cols, dtype)
+    # argmax over a vocab-sharded logits matrix == argmax over the gathered one
+    batch, shard = 33, 1000
+    logits = [torch.randn(batch, shard, generator=gen).bfloat16() for _ in range(world)]
+    full = torch.cat(logits, dim=-1).float()
+    pairs = []
+    for r, l in enumerate(logits):
+        v, i = l.float().max(dim=-1)
+        pairs.append(torch.stack([v, (i + r * shard).float()], dim=-1).cuda())
+    gathered = g.all_gather_lastdim(pairs)[0].view(batch, world, 2)
+    pick = gathered[:, :, 0].argmax(dim=-1, keepdim=True)
+    top = gathered[:, :, 1].gather(-1, pick).squeeze(-1).long().cpu()
+    assert torch.equal(full.gather(-1, top[:, None]).squeeze(-1), full.max(dim=-1).values)
+    g.check_health()
+
+
 @pytest.mark.parametrize("name", ["ag_tp2", "ag_tp4", "ag_tp8"])
 def test_all_gather_vs_vllm_golden(pkg, golden_dir, name):
     gold = dict(np.load(os.path.join(golden_dir, name + ".npz")))

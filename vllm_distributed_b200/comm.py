@@ -149,9 +149,10 @@ class B200Comm:
 
     def can_all_gather_lastdim(self, x: torch.Tensor) -> bool:
         row_bytes = x.shape[-1] * x.element_size()
-        return (x.is_cuda and x.is_contiguous() and row_bytes % 16 == 0 and x.numel() > 0
+        vec = 16 if row_bytes % 16 == 0 else 8 if row_bytes % 8 == 0 else 4
+        return (x.is_cuda and x.is_contiguous() and row_bytes % 4 == 0 and x.numel() > 0
                 and x.numel() * x.element_size() * self.world <= self.ag_bytes
-                and x.data_ptr() % 16 == 0)
+                and x.data_ptr() % vec == 0)
 
     def can_p2p(self, t: torch.Tensor) -> bool:
         nbytes = t.numel() * t.element_size()

@@ -731,15 +731,38 @@ int b200c_rms_norm(void* out, const void* x, const void* gamma, float eps, int t
   return local_norm(out, x, nullptr, nullptr, gamma, eps, tokens, hidden, dtype, stream);
 }
 
+}  // extern "C" (templates below need C++ linkage)
+
+template <int VEC>
+static int all_gather_launch(b200c_ctx* const* ctxs, int nemu, CopyParams* cp, size_t slab_words,
+                             cudaStream_t s) {
+  b200c_ctx* c0 = ctxs[0];
+  int g = 1;
+  if (nemu == 0) {
+    int rc = copy_grid(c0, slab_words, 0, all_gather_kernel<VEC>, &g);
+    if (rc) return rc;
+    return launch(all_gather_kernel<VEC>, dim3(g, 1, 1), 512, cp[0], s, false);
+  }
+  int rc = copy_grid(c0, slab_words, nemu, all_gather_kernel_emu<VEC>, &g);
+  if (rc) return rc;
+  EmuCopyParams ep;
+  memset(&ep, 0, sizeof(ep));
+  for (int r = 0; r < nemu; ++r) ep.r[r] = cp[r];
+  return launch(all_gather_kernel_emu<VEC>, dim3(g, nemu, 1), 512, ep, s, true);
+}
+
 static int all_gather_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
                            void* const* outs, int rows, size_t row_bytes, cudaStream_t s) {
   b200c_ctx* c0 = ctxs[0];
-  if (rows < 0 || row_bytes % 16) return fail(B200C_EINVAL, "row_bytes must be a multiple of 16");
+  if (rows < 0 || row_bytes % 4) return fail(B200C_EINVAL, "row_bytes must be a multiple of 4");
   if (rows == 0 || row_bytes == 0) return B200C_OK;
+  // widest word that divides a row (16-byte vectors for logits, 8 for [batch, 2] fp32 pairs)
+  const int vec = (row_bytes % 16 == 0) ? 16 : (row_bytes % 8 == 0) ? 8 : 4;
   const size_t out_bytes = (size_t)rows * row_bytes * c0->world;
   const int n = nemu ? nemu : 1;
   for (int r = 0; r < n; ++r)
-    if (!ins[r] || !outs[r] || !aligned16(ins[r]) || !aligned16(outs[r]))
+    if (!ins[r] || !outs[r] || (reinterpret_cast<uintptr_t>(ins[r]) % vec) ||
+        (reinterpret_cast<uintptr_t>(outs[r]) % vec))
       return fail(B200C_EINVAL, "null or misaligned pointer");
   if (c0->world == 1) {
     if (ins[0] != outs[0])
@@ -749,28 +772,23 @@ static int all_gather_impl(b200c_ctx* const* ctxs, int nemu, const void* const* 
   if (out_bytes > c0->ag_bytes)
     return fail(B200C_ETOOBIG, "all-gather output of %zu bytes exceeds ag_bytes %zu", out_bytes,
                 c0->ag_bytes);
-  const size_t slab_vecs = (size_t)rows * row_bytes / 16;
+  const size_t slab_words = (size_t)rows * row_bytes / vec;
   CopyParams cp[kMaxRanks];
   for (int r = 0; r < n; ++r) {
     fill_copy_params(ctxs[r], cp[r]);
     cp[r].in = ins[r];
     cp[r].out = outs[r];
     cp[r].rows = rows;
-    cp[r].row_vecs = row_bytes / 16;
+    cp[r].row_vecs = row_bytes / vec;
   }
-  int g = 1;
-  if (nemu == 0) {
-    int rc = copy_grid(c0, slab_vecs, 0, all_gather_kernel, &g);
-    if (rc) return rc;
-    return launch(all_gather_kernel, dim3(g, 1, 1), 512, cp[0], s, false);
+  switch (vec) {
+    case 16: return all_gather_launch<16>(ctxs, nemu, cp, slab_words, s);
+    case 8: return all_gather_launch<8>(ctxs, nemu, cp, slab_words, s);
+    default: return all_gather_launch<4>(ctxs, nemu, cp, slab_words, s);
   }
-  int rc = copy_grid(c0, slab_vecs, nemu, all_gather_kernel_emu, &g);
-  if (rc) return rc;
-  EmuCopyParams ep;
-  memset(&ep, 0, sizeof(ep));
-  for (int r = 0; r < nemu; ++r) ep.r[r] = cp[r];
-  return launch(all_gather_kernel_emu, dim3(g, nemu, 1), 512, ep, s, true);
 }
+
+extern "C" {
 
 int b200c_all_gather_lastdim(b200c_ctx* c, const void* in, void* out, int rows, size_t row_bytes,
                              void* stream) {

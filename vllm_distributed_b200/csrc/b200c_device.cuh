@@ -82,6 +82,43 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
+// Narrow (4- and 8-byte) copies for rows that are not a multiple of 16 bytes, e.g. the
+// [batch, 2] fp32 (value, index) pairs of the vocab-parallel argmax.
+template <int BYTES>
+struct Word;
+template <>
+struct Word<16> {
+  using type = uint4;
+  static __device__ __forceinline__ uint4 ld(const void* p) { return ld_stream_v4(p); }
+  static __device__ __forceinline__ uint4 poll(const void* p) { return ld_poll_v4(p); }
+  static __device__ __forceinline__ void push(void* p, const uint4& v) { st_push_v4(p, v); }
+  static __device__ __forceinline__ void st(void* p, const uint4& v) { st_v4(p, v); }
+};
+template <>
+struct Word<8> {
+  using type = uint2;
+  static __device__ __forceinline__ uint2 ld(const void* p) { return *reinterpret_cast<const uint2*>(p); }
+  static __device__ __forceinline__ uint2 poll(const void* p) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+  }
+  static __device__ __forceinline__ void push(void* p, const uint2& v) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+  }
+  static __device__ __forceinline__ void st(void* p, const uint2& v) { *reinterpret_cast<uint2*>(p) = v; }
+};
+template <>
+struct Word<4> {
+  using type = uint32_t;
+  static __device__ __forceinline__ uint32_t ld(const void* p) { return *reinterpret_cast<const uint32_t*>(p); }
+  static __device__ __forceinline__ uint32_t poll(const void* p) { return ld_volatile_u32(reinterpret_cast<const uint32_t*>(p)); }
+  static __device__ __forceinline__ void push(void* p, const uint32_t& v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+  }
+  static __device__ __forceinline__ void st(void* p, const uint32_t& v) { *reinterpret_cast<uint32_t*>(p) = v; }
+};
+
 // ---- arrival marker helpers ----------------------------------------------------------------
 
 __device__ __forceinline__ bool not_arrived(const uint4& v) {

@@ -792,26 +792,28 @@ __device__ __forceinline__ void wait_flag_ge(const uint32_t* f, uint32_t want, c
   }
 }
 
+template <int VEC>
 __device__ __forceinline__ void all_gather_body(const CopyParams& p) {
+  using W = Word<VEC>;
   const uint32_t seq = p.st->ag_seq;
   const uint32_t par = seq & 1u;
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
-  const size_t rv = (size_t)p.row_vecs;
+  const size_t rv = (size_t)p.row_vecs;  // VEC-byte words per slab row
   const size_t slab_vecs = rv * (size_t)p.rows;
   const size_t stage_off = p.g.ag_off + (size_t)par * p.g.ag_stride;
   SpinGuard sg;
 
-  // push my slab: vector (row, c) -> staging[(row*world + rank)*rv + c] on every peer;
+  // push my slab: word (row, c) -> staging[(row*world + rank)*rv + c] on every peer;
   // my own slab goes straight to `out`.
   for (size_t i = gtid; i < slab_vecs; i += gsize) {
     const size_t row = i / rv, c = i - row * rv;
-    const uint4 v = ld_stream_v4((const char*)p.in + i * 16);
-    const size_t dst = ((row * p.world + p.rank) * rv + c) * 16;
+    const typename W::type v = W::ld((const char*)p.in + i * VEC);
+    const size_t dst = ((row * p.world + p.rank) * rv + c) * VEC;
 #pragma unroll
     for (int r = 0; r < kMaxRanks; ++r)
-      if (r < p.world && r != p.rank) st_push_v4(p.arena[r] + stage_off + dst, v);
-    st_v4((char*)p.out + dst, v);
+      if (r < p.world && r != p.rank) W::push(p.arena[r] + stage_off + dst, v);
+    W::st((char*)p.out + dst, v);
   }
   __threadfence_system();
   __syncthreads();
@@ -832,8 +834,8 @@ __device__ __forceinline__ void all_gather_body(const CopyParams& p) {
     wait_flag_ge(ctrl_flag(p.arena[p.rank], kAgFlagOff, (int)par * kMaxRanks + src), seq + 1, p, sg);
     for (size_t i = gtid; i < slab_vecs; i += gsize) {
       const size_t row = i / rv, c = i - row * rv;
-      const size_t off = ((row * p.world + src) * rv + c) * 16;
-      st_v4((char*)p.out + off, ld_poll_v4(stage + off));
+      const size_t off = ((row * p.world + src) * rv + c) * VEC;
+      W::st((char*)p.out + off, W::poll(stage + off));
     }
   }
   __syncthreads();
@@ -848,12 +850,14 @@ __device__ __forceinline__ void all_gather_body(const CopyParams& p) {
   }
 }
 
+template <int VEC>
 __global__ void __launch_bounds__(512) all_gather_kernel(const __grid_constant__ CopyParams p) {
-  all_gather_body(p);
+  all_gather_body<VEC>(p);
 }
+template <int VEC>
 __global__ void __launch_bounds__(512)
     all_gather_kernel_emu(const __grid_constant__ EmuCopyParams ep) {
-  all_gather_body(ep.r[blockIdx.y]);
+  all_gather_body<VEC>(ep.r[blockIdx.y]);
 }
 
 // ---- pipeline-stage send / recv (mailbox + ready flag + credit) ---------------------------------
