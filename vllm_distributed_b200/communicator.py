@@ -160,8 +160,18 @@ class B200Communicator(CudaCommunicator):
         tensor.record_stream(recv_stream)
         return tensor, StreamHandle(recv_stream, wait_needed=True)
 
+    def check_health(self) -> None:
+        """Raises B200CError if a device-side wait on a peer ever timed out (host-synchronous).
+        The reference's barrier would have hung instead (vllm_custom_all_reduce.cuh:190-211)."""
+        if self.b200 is not None:
+            self.b200.check_health()
+
     def destroy(self):
         if self.b200 is not None:
+            try:
+                self.b200.check_health()
+            except Exception as e:  # noqa: BLE001 -- report, then still release the arenas
+                logger.error("b200c: %s", e)
             self.b200.close()
             self.b200 = None
         super().destroy()
