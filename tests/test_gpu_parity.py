@@ -63,7 +63,8 @@ def check_norm(y_gpu, y_ref, dtype):
 # ---- TP=1: the local norm kernels ------------------------------------------------------------
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
-@pytest.mark.parametrize("shape", [(1, 896), (5, 896), (64, 4096), (7, 8192), (3, 16384), (2, 8)])
+@pytest.mark.parametrize("shape", [(1, 896), (5, 896), (64, 4096), (7, 8192), (3, 16384), (2, 8),
+                                   (601, 896), (1203, 4096)])  # the last two: 2 and 4 rows per trip
 def test_world1_fused_add_rms_norm(pkg, dtype, shape):
     comm, _, _ = pkg
     if dtype == torch.float32 and shape[1] > 8192:

@@ -343,6 +343,15 @@ int launch_ar_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int want
 template <typename T>
 int launch_norm_only(const RankParams& rp, int vpt, int threads, int sm_count, cudaStream_t s,
                      bool pdl) {
+  if (vpt == 1 && rp.tokens >= 8 * sm_count) {
+    // bandwidth regime with narrow rows: four rows per trip (see norm_kernel_rows)
+    const int g = std::max(1, std::min((rp.tokens + 3) / 4, sm_count * 8));
+    return launch(norm_kernel_rows<T, 4>, dim3(g, 1, 1), threads, rp, s, false, pdl);
+  }
+  if (vpt == 1 && rp.tokens >= 4 * sm_count) {
+    const int g = std::max(1, std::min((rp.tokens + 1) / 2, sm_count * 16));
+    return launch(norm_kernel_rows<T, 2>, dim3(g, 1, 1), threads, rp, s, false, pdl);
+  }
   const int g = std::max(1, std::min(rp.tokens, sm_count * 16));
   switch (vpt) {
     case 1: return launch(norm_kernel<T, 1>, dim3(g, 1, 1), threads, rp, s, false, pdl);
@@ -374,8 +383,14 @@ int check_rows(int tokens, int hidden, int dtype, int* hv) {
 }
 
 int sm_count_of_current_device(int* dev, int* sms) {
+  static int cached[64] = {};  // asked on every ctx-less norm call
   CUDA_TRY(cudaGetDevice(dev));
+  if (*dev >= 0 && *dev < 64 && cached[*dev] > 0) {
+    *sms = cached[*dev];
+    return B200C_OK;
+  }
   CUDA_TRY(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, *dev));
+  if (*dev >= 0 && *dev < 64) cached[*dev] = *sms;
   return B200C_OK;
 }
 

@@ -250,6 +250,33 @@ __device__ __forceinline__ float block_sum(float v, float* smem /* 64 floats */,
   return t;  // every warp reduces the same 32 partials in the same order
 }
 
+// R independent block-wide sums behind ONE barrier (R rows per trip in the HBM-bound norm).
+// smem: 2 parities x R x 32 floats.
+template <int R>
+__device__ __forceinline__ void block_sum_multi(float (&v)[R], float* smem, int& parity) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int k = 0; k < R; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  float* bank = smem + parity * (R * 32);
+  parity ^= 1;
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < R; ++k) bank[k * 32 + warp] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    float t = (lane < nwarps) ? bank[k * 32 + lane] : 0.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    v[k] = t;
+  }
+}
+
 // ---- thread-block clusters: rows split over the CTAs of a cluster -------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

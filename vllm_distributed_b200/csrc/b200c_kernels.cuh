@@ -757,6 +757,73 @@ __global__ void __launch_bounds__(512) norm_kernel(const __grid_constant__ RankP
   }
 }
 
+// Narrow rows (one vector per thread) in the bandwidth regime: R rows per trip.  Every thread
+// keeps 2R independent 16-byte loads in flight, only the raw vectors stay in registers across
+// the barrier (x = s + r is recomputed afterwards: a few adds instead of 8 live floats per row),
+// and the R block reductions share one barrier.  Same per-row arithmetic and reduction tree as
+// norm_kernel<T,1>, hence the same bits.
+template <typename T, int R>
+__global__ void __launch_bounds__(512, 2) norm_kernel_rows(const __grid_constant__ RankParams p) {
+  constexpr int EPV = VecOps<T>::EPV;
+  __shared__ float smem[2 * R * 32];
+  pdl_launch_dependents();
+  const int c = threadIdx.x;
+  const bool valid = c < p.hv;
+  uint4 gam = make_uint4(0, 0, 0, 0);
+  if (valid) gam = ld_v4((const char*)p.gamma + (size_t)c * 16);
+  pdl_wait();
+  int parity = 0;
+  const bool has_res = p.res_in != nullptr;
+  for (int row = R * blockIdx.x; row < p.tokens; row += R * gridDim.x) {
+    uint4 s[R], r[R];
+    float ss[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      ss[k] = 0.0f;
+      if (valid && row + k < p.tokens) {
+        const size_t idx = (size_t)(row + k) * p.hv + c;
+        s[k] = ld_stream_v4((const char*)p.in + idx * 16);
+        if (has_res) r[k] = ld_stream_v4((const char*)p.res_in + idx * 16);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      if (valid && row + k < p.tokens) {
+        float x[EPV];
+        VecOps<T>::to_float(s[k], x);
+        if (has_res) {
+          float rr[EPV];
+          VecOps<T>::to_float(r[k], rr);
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) x[e] = x[e] + rr[e];
+          st_v4((char*)p.res_out + ((size_t)(row + k) * p.hv + c) * 16, VecOps<T>::from_float(x));
+        }
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) ss[k] += x[e] * x[e];
+      }
+    }
+    block_sum_multi<R>(ss, smem, parity);
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      if (valid && row + k < p.tokens) {
+        float x[EPV], g[EPV], y[EPV];
+        VecOps<T>::to_float(s[k], x);
+        if (has_res) {
+          float rr[EPV];
+          VecOps<T>::to_float(r[k], rr);
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) x[e] = x[e] + rr[e];
+        }
+        const float rs = 1.0f / sqrtf(ss[k] / (float)p.hidden + p.eps);
+        VecOps<T>::to_float(gam, g);
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) y[e] = VecOps<T>::round_trip(x[e] * rs) * g[e];
+        st_v4((char*)p.norm_out + ((size_t)(row + k) * p.hv + c) * 16, VecOps<T>::from_float(y));
+      }
+    }
+  }
+}
+
 // ---- all-gather along the last dim (byte-exact; flag protocol) -----------------------------------
 // Staging layout in every rank's arena = the final [rows][world][row_bytes] layout, double
 // buffered on the call parity.  Each rank pushes its slab into all peers' staging, fences,
