@@ -1,0 +1,70 @@
+"""The reference launcher's worker bring-up, UNMODIFIED, on the installed vLLM with the shim and the
+plugin: launch.CustomExecutor spawns a local worker over its own RPC (launch.py:153-190, rpc.py,
+rpc_reader.py), WorkerWrapper clobbers local_rank (launch.py:510-520), init_worker / init_device /
+load_model are driven by name (launch.py:290-292), collective_rpc and execute_model return from the
+output rank (launch.py:322-384), and the b200c plugin is registered inside the worker process.
+CPU-only: the worker class is a stub (tests/stub_worker.py); the real Worker needs a GPU.
+Runs only where the reference checkout is mounted."""
+import os
+import signal
+import subprocess
+import sys
+import tempfile
+
+import pytest
+
+REF_SRC = "/root/reference/src"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TESTS = os.path.dirname(os.path.abspath(__file__))
+
+SCRIPT = r'''
+import json, os, socket, sys, tempfile
+ROOT, REF, TESTS = %r, %r, %r
+sys.path[:0] = [ROOT, REF, TESTS]
+with socket.socket() as s:
+    s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+os.environ["VLLM_SERVER_PORT"] = str(port)
+from vllm_distributed_b200 import launch_shim
+launch_shim.install()
+import launch                                   # the reference's own module, unmodified
+from vllm.config import DeviceConfig, ModelConfig, ParallelConfig, VllmConfig
+d = tempfile.mkdtemp()
+json.dump(dict(architectures=["LlamaForCausalLM"], model_type="llama", hidden_size=256,
+               intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+               num_key_value_heads=4, vocab_size=1024, rms_norm_eps=1e-5,
+               max_position_embeddings=512, torch_dtype="bfloat16"), open(d + "/config.json", "w"))
+cfg = VllmConfig(model_config=ModelConfig(model=d, skip_tokenizer_init=True, dtype="bfloat16", max_model_len=128),
+                 parallel_config=ParallelConfig(worker_cls="stub_worker.StubWorker"),
+                 device_config=DeviceConfig(device="cpu"))
+ex = launch.CustomExecutor(cfg)
+assert ex.world_size == 1 and ex.output_rank == 0
+(rank, local_rank, echo, calls), = ex.collective_rpc("ping", args=(7,))
+assert (rank, echo) == (0, 7) and local_rank == 0        # -1 from the head was clobbered
+assert calls == ["__init__", "init_device", "load_model"], calls
+assert ex.execute_model("sched-out") == {"rank": 0, "echo": "sched-out"}
+ex.check_health()
+print("BRINGUP OK", flush=True)
+os._exit(0)
+'''
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_SRC), reason="reference checkout not mounted")
+def test_reference_executor_brings_up_a_worker_under_the_shim():
+    with tempfile.TemporaryDirectory() as td:
+        log = os.path.join(td, "run.log")
+        with open(log, "w") as f:
+            p = subprocess.Popen([sys.executable, "-u", "-c", SCRIPT % (ROOT, REF_SRC, TESTS)],
+                                 stdout=f, stderr=subprocess.STDOUT, start_new_session=True,
+                                 env=dict(os.environ, PYTHONPATH=os.pathsep.join([ROOT, TESTS])))
+            try:
+                rc = p.wait(timeout=240)
+            finally:
+                try:
+                    os.killpg(p.pid, signal.SIGKILL)   # the launcher's daemon worker, if still around
+                except ProcessLookupError:
+                    pass
+        text = open(log).read()
+    assert rc == 0, text[-3000:]
+    assert "BRINGUP OK" in text
+    assert "b200c plugin registered" in text             # ... inside the launcher's worker process
+    assert "WorkerWrapper created for rpc_rank 0, local_rank 0" in text
