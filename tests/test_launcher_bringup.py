@@ -68,3 +68,61 @@ def test_reference_executor_brings_up_a_worker_under_the_shim():
     assert "BRINGUP OK" in text
     assert "b200c plugin registered" in text             # ... inside the launcher's worker process
     assert "WorkerWrapper created for rpc_rank 0, local_rank 0" in text
+
+
+SCRIPT_REMOTE = r'''
+import json, os, signal, socket, subprocess, sys, tempfile
+ROOT, REF, TESTS = %r, %r, %r
+sys.path[:0] = [ROOT, REF, TESTS]
+with socket.socket() as s:
+    s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+os.environ["VLLM_SERVER_PORT"] = str(port)
+os.environ["PYTHONPATH"] = os.pathsep.join([ROOT, TESTS])
+from vllm_distributed_b200 import launch_shim
+launch_shim.install()
+import launch
+from vllm.config import DeviceConfig, ModelConfig, ParallelConfig, VllmConfig
+d = tempfile.mkdtemp()
+json.dump(dict(architectures=["LlamaForCausalLM"], model_type="llama", hidden_size=256,
+               intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+               num_key_value_heads=4, vocab_size=1024, rms_norm_eps=1e-5,
+               max_position_embeddings=512, torch_dtype="bfloat16"), open(d + "/config.json", "w"))
+cfg = VllmConfig(model_config=ModelConfig(model=d, skip_tokenizer_init=True, dtype="bfloat16", max_model_len=128),
+                 parallel_config=ParallelConfig(worker_cls="stub_worker.StubWorker", pipeline_parallel_size=2,
+                                                distributed_executor_backend="external_launcher"),
+                 device_config=DeviceConfig(device="cpu"))
+# the second "host": the reference's own `launch.py remote <ip>` entry point, through the shim
+remote = subprocess.Popen([sys.executable, "-u", "-m", "vllm_distributed_b200.launch_shim",
+                           os.path.join(REF, "launch.py"), "remote", "127.0.0.1"], env=dict(os.environ))
+ex = launch.CustomExecutor(cfg)          # stage 0 is filled locally, stage 1 from the remote node
+assert ex.world_size == 2 and ex.output_rank == 1      # first TP worker of the LAST pipeline stage
+res = ex.collective_rpc("ping", args=(7,))
+assert [r[0] for r in res] == [0, 1] and all(r[3] == ["__init__", "init_device", "load_model"] for r in res), res
+assert ex.execute_model("sched-out") == {"rank": 1, "echo": "sched-out"}
+print("BRINGUP REMOTE OK", flush=True)
+os._exit(0)
+'''
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_SRC), reason="reference checkout not mounted")
+def test_reference_executor_fills_a_pipeline_stage_from_a_remote_node():
+    """PP=2: stage 0 from a local worker, stage 1 from a node started with the launcher's own
+    `launch.py remote <ip>` (launch.py:543-632) over TCP + cloudpickle RPC."""
+    with tempfile.TemporaryDirectory() as td:
+        log = os.path.join(td, "run.log")
+        with open(log, "w") as f:
+            p = subprocess.Popen([sys.executable, "-u", "-c", SCRIPT_REMOTE % (ROOT, REF_SRC, TESTS)],
+                                 stdout=f, stderr=subprocess.STDOUT, start_new_session=True,
+                                 env=dict(os.environ, PYTHONPATH=os.pathsep.join([ROOT, TESTS])))
+            try:
+                rc = p.wait(timeout=300)
+            finally:
+                try:
+                    os.killpg(p.pid, signal.SIGKILL)   # head, remote node and their workers
+                except ProcessLookupError:
+                    pass
+        text = open(log).read()
+    assert rc == 0, text[-3000:]
+    assert "BRINGUP REMOTE OK" in text
+    assert text.count("b200c plugin registered") >= 2     # in the local AND the remote worker
+    assert "WorkerWrapper created for rpc_rank 1, local_rank 0" in text
