@@ -22,5 +22,8 @@ class StubWorker:
     def execute_model(self, scheduler_output):
         return {"rank": self.rank, "echo": scheduler_output}
 
+    def sample_tokens(self, grammar_output):
+        return {"rank": self.rank, "sampled": grammar_output}
+
     def shutdown(self):
         pass

@@ -79,9 +79,10 @@ with socket.socket() as s:
 os.environ["VLLM_SERVER_PORT"] = str(port)
 os.environ["PYTHONPATH"] = os.pathsep.join([ROOT, TESTS])
 from vllm_distributed_b200 import launch_shim
-launch_shim.install()
-import launch
+launch = launch_shim.load_launcher(os.path.join(REF, "launch.py"))   # shim + plugin + 0.22 executor protocol
 from vllm.config import DeviceConfig, ModelConfig, ParallelConfig, VllmConfig
+from vllm.v1.executor.abstract import Executor
+assert launch.CustomExecutor.supports_pp and issubclass(launch.CustomExecutor, Executor)
 d = tempfile.mkdtemp()
 json.dump(dict(architectures=["LlamaForCausalLM"], model_type="llama", hidden_size=256,
                intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
@@ -99,6 +100,10 @@ assert ex.world_size == 2 and ex.output_rank == 1      # first TP worker of the 
 res = ex.collective_rpc("ping", args=(7,))
 assert [r[0] for r in res] == [0, 1] and all(r[3] == ["__init__", "init_device", "load_model"] for r in res), res
 assert ex.execute_model("sched-out") == {"rank": 1, "echo": "sched-out"}
+# vLLM 0.22 samples in a second RPC: it must be answered by the last stage too
+assert ex.sample_tokens("grammar") == {"rank": 1, "sampled": "grammar"}
+fut = ex.sample_tokens("g2", non_block=True)
+assert fut.result(timeout=30) == {"rank": 1, "sampled": "g2"}
 print("BRINGUP REMOTE OK", flush=True)
 os._exit(0)
 '''

@@ -23,7 +23,6 @@ from __future__ import annotations
 
 import importlib
 import os
-import runpy
 import sys
 import types
 
@@ -112,17 +111,58 @@ def install() -> dict[str, str]:
     return report
 
 
+def adapt_executor(executor_cls) -> None:
+    """Bring the launcher's CustomExecutor up to the executor protocol of vLLM 0.22
+    (vllm/v1/executor/abstract.py:44-45, 221-247) without touching its source:
+      * supports_pp: the engine refuses pipeline parallelism otherwise (arg_utils.py:2265-2268);
+      * sample_tokens: 0.22 samples in a second RPC; like execute_model (launch.py:322-336) the
+        answer must come from the first TP worker of the LAST pipeline stage (output_rank), not
+        from worker 0 as the base class would take it.
+    """
+    executor_cls.supports_pp = True
+
+    def sample_tokens(self, grammar_output, non_block: bool = False):
+        (output,) = self.collective_rpc("sample_tokens", args=(grammar_output,),
+                                        unique_reply_rank=self.output_rank, non_block=non_block)
+        return output
+
+    if "sample_tokens" not in executor_cls.__dict__:
+        executor_cls.sample_tokens = sample_tokens
+
+
+def load_launcher(script: str):
+    """Install the shim, register the plugin, import the launcher file as module `launch` and
+    adapt its executor.  Returns the module: `mod.CustomExecutor` can be handed to vLLM as
+    `distributed_executor_backend`, `mod.main()` is the launcher's own CLI."""
+    import importlib.util
+    script = os.path.abspath(script)
+    install()
+    from . import plugin
+    plugin.register()
+    src_dir = os.path.dirname(script)
+    if src_dir not in sys.path:
+        sys.path.insert(0, src_dir)  # launch.py imports its siblings rpc / rpc_reader
+    name = os.path.splitext(os.path.basename(script))[0]
+    if name in sys.modules and getattr(sys.modules[name], "__file__", None) == script:
+        mod = sys.modules[name]
+    else:
+        spec = importlib.util.spec_from_file_location(name, script)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[name] = mod  # multiprocessing pickles worker_main by module name
+        spec.loader.exec_module(mod)
+    if hasattr(mod, "CustomExecutor"):
+        adapt_executor(mod.CustomExecutor)
+    return mod
+
+
 def main(argv: list[str] | None = None) -> None:
     argv = list(sys.argv[1:] if argv is None else argv)
     if not argv:
         raise SystemExit("usage: python -m vllm_distributed_b200.launch_shim <launch.py> [args...]")
     script = os.path.abspath(argv[0])
-    install()
-    from . import plugin
-    plugin.register()
-    sys.path.insert(0, os.path.dirname(script))  # launch.py imports its siblings rpc / rpc_reader
+    mod = load_launcher(script)
     sys.argv = [script] + argv[1:]
-    runpy.run_path(script, run_name="__main__")
+    mod.main()
 
 
 if __name__ == "__main__":
