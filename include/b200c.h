@@ -55,6 +55,7 @@ extern "C" {
 #define B200C_TUNE_LINK_BLOCKS 6       /* two-shot CTAs doing link work; 0 = half the grid */
 #define B200C_TUNE_PDL 7               /* programmatic dependent launch on/off (default on) */
 #define B200C_TUNE_ONESHOT_SPLIT 8     /* CTAs (cluster size) per row, one-shot fused: 0 auto, 1 none */
+#define B200C_TUNE_DEBUG_EPOCH 9       /* test hook, host-synchronous: read / jump the call counter     */
 
 typedef struct b200c_ctx b200c_ctx;
 

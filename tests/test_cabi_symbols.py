@@ -44,5 +44,5 @@ def test_header_constants_match_binding():
     for k in ("BF16", "F16", "F32", "AUTO", "ONESHOT", "TWOSHOT", "EINVAL", "ECUDA", "ETOOBIG",
               "ETIMEOUT", "ENOMEM", "TUNE_ONESHOT_MAX_BYTES", "TUNE_ONESHOT_BLOCKS",
               "TUNE_TWOSHOT_BLOCKS", "TUNE_SPIN_TIMEOUT_MS", "TUNE_COPY_BLOCKS", "TUNE_LINK_BLOCKS",
-              "TUNE_PDL", "TUNE_ONESHOT_SPLIT"):
+              "TUNE_PDL", "TUNE_ONESHOT_SPLIT", "TUNE_DEBUG_EPOCH"):
         assert int(consts[k]) == getattr(C, k), k

@@ -62,3 +62,37 @@ def test_random_call_sequence(world):
         assert bad == 0, f"first mismatch at call {it} ({kind}), world {world}"
     g.check_health()
     g.close()
+
+
+def test_call_counter_wraps_without_breaking_the_region_rotation():
+    """The 32-bit call counter wraps after 2^32 calls (days of decode).  0xffffffff is skipped so
+    that region = counter % 3 keeps cycling 1, 2, 0 across the wrap."""
+    from vllm_distributed_b200 import _cabi as C
+    from vllm_distributed_b200.emu import EmuGroup
+    world = 4
+    g = EmuGroup(world, "cuda:0", max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=64 << 10)
+    g.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, 3000)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+
+    def one_call(i):
+        xs = [torch.randn(4 + i % 5, 4096, device="cuda", generator=gen).bfloat16() for _ in range(world)]
+        res = torch.randn_like(xs[0])
+        gamma = torch.randn(4096, device="cuda", generator=gen).bfloat16()
+        ys, rs = g.all_reduce_add_rmsnorm(xs, [res.clone() for _ in range(world)], gamma, 1e-5,
+                                          variant=1 + i % 2)
+        x32 = _ref_sum(xs).float() + res.float()
+        assert all(torch.equal(r, x32.bfloat16()) for r in rs), f"call {i}"
+        assert all(torch.equal(y, ys[0]) for y in ys)
+
+    for i in range(3):                       # counter is now 3: region 0 is next
+        one_call(i)
+    assert g.ranks[0].get_tuning(C.TUNE_DEBUG_EPOCH) == 3
+    start = 0xFFFFFFF0 - (0xFFFFFFF0 % 3)    # a multiple of 3 just below the wrap: same region next
+    g.set_tuning(C.TUNE_DEBUG_EPOCH, start)
+    for i in range(40):                      # crosses 2^32
+        one_call(i)
+    after = g.ranks[0].get_tuning(C.TUNE_DEBUG_EPOCH)
+    assert after < 64, hex(after)            # wrapped
+    assert after == (start + 40) - 0xFFFFFFFF   # exactly one value (0xffffffff) was skipped
+    g.check_health()
+    g.close()

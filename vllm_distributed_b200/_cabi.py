@@ -20,7 +20,7 @@ AUTO, ONESHOT, TWOSHOT = 0, 1, 2
 OK, EINVAL, ECUDA, ETOOBIG, ETIMEOUT, ENOMEM = 0, -1, -2, -3, -4, -5
 TUNE_ONESHOT_MAX_BYTES, TUNE_ONESHOT_BLOCKS, TUNE_TWOSHOT_BLOCKS = 1, 2, 3
 TUNE_SPIN_TIMEOUT_MS, TUNE_COPY_BLOCKS = 4, 5
-TUNE_LINK_BLOCKS, TUNE_PDL, TUNE_ONESHOT_SPLIT = 6, 7, 8
+TUNE_LINK_BLOCKS, TUNE_PDL, TUNE_ONESHOT_SPLIT, TUNE_DEBUG_EPOCH = 6, 7, 8, 9
 NOALLOC_MAX_BYTES = 64 * 1024
 
 Handle = c_ubyte * IPC_HANDLE_BYTES

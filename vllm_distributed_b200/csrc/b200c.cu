@@ -653,6 +653,14 @@ int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
     case B200C_TUNE_LINK_BLOCKS: c->link_blocks = (int)std::max<long long>(0, v); break;
     case B200C_TUNE_PDL: c->pdl = v != 0; break;
     case B200C_TUNE_ONESHOT_SPLIT: c->oneshot_split = (int)std::max<long long>(0, std::min<long long>(8, v)); break;
+    case B200C_TUNE_DEBUG_EPOCH: {
+      // test hook (host-synchronous): jump the all-reduce call counter, e.g. to just below 2^32
+      if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
+      const unsigned long long w = (unsigned long long)(uint32_t)v << 32;
+      CUDA_TRY(cudaDeviceSynchronize());
+      CUDA_TRY(cudaMemcpy(&c->st->call, &w, sizeof(w), cudaMemcpyHostToDevice));
+      break;
+    }
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;
@@ -669,6 +677,14 @@ int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
     case B200C_TUNE_LINK_BLOCKS: *v = c->link_blocks; break;
     case B200C_TUNE_PDL: *v = c->pdl; break;
     case B200C_TUNE_ONESHOT_SPLIT: *v = c->oneshot_split; break;
+    case B200C_TUNE_DEBUG_EPOCH: {
+      if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
+      unsigned long long w = 0;
+      CUDA_TRY(cudaDeviceSynchronize());
+      CUDA_TRY(cudaMemcpy(&w, &c->st->call, sizeof(w), cudaMemcpyDeviceToHost));
+      *v = (long long)(w >> 32);
+      break;
+    }
     default: return fail(B200C_EINVAL, "unknown tuning key %d", key);
   }
   return B200C_OK;

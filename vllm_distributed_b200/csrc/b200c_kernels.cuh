@@ -162,8 +162,9 @@ __device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* /
   cs.ticket = 0;
   const uint32_t* hi = reinterpret_cast<const uint32_t*>(&p.st->call) + 1;  // little endian
   cs.epoch = ld_volatile_u32(hi);
-  if (cs.epoch == 0xffffffffu) __trap();  // forces the load to have returned here
-  __syncthreads();
+  // The barrier takes a predicate computed from the loaded value, so no thread can arrive
+  // before its epoch load has returned (the result of the OR itself is irrelevant).
+  (void)__syncthreads_or(cs.epoch == 0xffffffffu);
   if (threadIdx.x == 0) cs.ticket = (uint32_t)atomicAdd(&p.st->call, 1ull);
   return cs;
 }
@@ -174,7 +175,10 @@ __device__ __forceinline__ void end_call(const RankParams& p, const CallState& c
     const uint32_t b = cs.epoch % 3u;
     p.st->dirty_lo[b] = dlo;
     p.st->dirty_hi[b] = dhi;
-    p.st->call = (unsigned long long)(cs.epoch + 1) << 32;
+    // 0xffffffff is a multiple of 3: wrapping from 0xfffffffe straight to 0 keeps the region
+    // sequence ... 1, 2, 0 ... intact after 2^32 calls (about a week of 70B decode)
+    const uint32_t next = (cs.epoch + 1u == 0xffffffffu) ? 0u : cs.epoch + 1u;
+    p.st->call = (unsigned long long)next << 32;
   }
 }
 
@@ -458,7 +462,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
 
   const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
   const uint32_t epoch = cs.epoch;
-  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t nvec = (size_t)p.nvec;
   const size_t chunk = (nvec + p.world - 1) / p.world;  // two-shot: vectors owned per rank
   char* my_lo = lam_region(p, p.rank, b);
@@ -561,7 +565,7 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
     v0 = ld_stream_v4((const char*)p.in + ((size_t)group * p.hv + c) * 16);
   const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
   const uint32_t epoch = cs.epoch;
-  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t nvec = (size_t)p.nvec;
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
@@ -659,7 +663,7 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
   pdl_wait();
   const CallState cs = begin_call(p, &s_epoch);
   const uint32_t epoch = cs.epoch;
-  const uint32_t b = epoch % 3u, pb = (epoch + 2u) % 3u;
+  const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
   const size_t nvec = (size_t)p.nvec;
