@@ -942,9 +942,10 @@ __device__ __forceinline__ void send_body(const CopyParams& p) {
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t gsize = (size_t)gridDim.x * blockDim.x;
   SpinGuard sg;
-  // credit[dst][slot] counts consumed messages of that slot: need >= m-1 (message m-2 done)
-  if (m >= 2)
-    wait_flag_ge(ctrl_flag(p.arena[p.rank], kP2pCreditOff, p.peer * 2 + (int)slot), m - 1, p, sg);
+  // credit[dst][slot] = index + 1 of the last message consumed from that slot: message m needs
+  // m-2 done, i.e. credit >= m-1.  The comparison is modular (signed difference), so it also
+  // holds for the first two messages (credit 0 vs m-1 = -1, 0) and across a 2^32 wrap.
+  wait_flag_ge(ctrl_flag(p.arena[p.rank], kP2pCreditOff, p.peer * 2 + (int)slot), m - 1, p, sg);
   char* box = p.arena[p.peer] + p.g.p2p_off + ((size_t)p.rank * 2 + slot) * p.g.p2p_stride;
   for (size_t i = gtid; i < (size_t)p.nvec; i += gsize)
     st_push_v4(box + i * 16, ld_stream_v4((const char*)p.in + i * 16));
