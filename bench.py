@@ -41,6 +41,17 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_REAL_STDOUT_FD = None  # set by main() while fd 1 is pointed at stderr
+
+
+def real_print(line: str) -> None:
+    """Write one line to the process's real stdout (the JSON contract), even mid-run."""
+    if _REAL_STDOUT_FD is None:
+        print(line, flush=True)
+    else:
+        os.write(_REAL_STDOUT_FD, (line + "\n").encode())
+
+
 def model_shape(n_gpus: int) -> dict:
     if n_gpus <= 2:
         return dict(model="llama3-8b-shaped", hidden=4096, layers=32, vocab=128256, eps=1e-5)
@@ -53,6 +64,22 @@ def measured_peaks() -> tuple[float, str]:
         return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
     except Exception:
         return HBM_FALLBACK_GBS, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def workload_config(shp: dict, n: int, B: int, variant: str) -> dict:
+    """The `config` object of the JSON line; both arms print the same one for the same flags."""
+    calls = 2 * shp["layers"] + 1
+    return {
+        "workload": f"{shp['model']} TP={n} decode hot path, batch {B}: {calls} x "
+                    + ("fused residual-add+RMSNorm" if n == 1 else
+                       "fused all-reduce+residual-add+RMSNorm + 1 lm_head all-gather")
+                    + f" on [{B},{shp['hidden']}] bf16",
+        "hidden": shp["hidden"], "layers": shp["layers"], "vocab": shp["vocab"], "batch": B, "tp": n,
+        "calls_per_step": calls + (1 if n > 1 else 0),
+        "l2": "256 MiB buffer rewritten between timed steps (untimed) to flush the 126 MB L2",
+        "execution": "step captured once as a CUDA graph, replayed per timed step",
+        "variant": variant,
+    }
 
 
 class ClockSampler:
@@ -134,11 +161,16 @@ def run_ours(args) -> dict:
     S = B * H * 2
 
     cpu_group = None
+    extras = n > 1 and not args.no_extras
+    big_tokens = 4096  # the bandwidth-regime point of the north star: [4096, H] = 64 MiB at H = 8192
     if n > 1:
         dist.init_process_group(backend="nccl", device_id=dev)
         cpu_group = dist.new_group(backend="gloo")
-        comm = bc.B200Comm.from_process_group(cpu_group, dev, max_bytes=max(S, 1 << 20),
-                                              ag_bytes=max(B * V * 2, 1 << 20), p2p_bytes=1 << 20)
+        max_bytes = max(S, 1 << 20, big_tokens * H * 2 if extras else 0)
+        comm = bc.B200Comm.from_process_group(cpu_group, dev, max_bytes=max_bytes,
+                                              ag_bytes=max(B * V * 2, 1 << 20), p2p_bytes=1 << 20,
+                                              device_group=dist.group.WORLD)
+        log(f"[rank {rank}] arenas up, NVLS multicast {'attached' if comm.nvls else 'not available'}")
     else:
         comm = bc.B200Comm(0, 1, None, 0, 0, 0, dev)
 
@@ -157,7 +189,7 @@ def run_ours(args) -> dict:
     logits_local = logits_host.to(dev)
     logits_full = torch.empty(B, V, dtype=torch.bfloat16, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    variant = {"auto": C.AUTO, "oneshot": C.ONESHOT, "twoshot": C.TWOSHOT}[args.variant]
+    variant = {"auto": C.AUTO, "oneshot": C.ONESHOT, "twoshot": C.TWOSHOT, "nvls": C.NVLS}[args.variant]
 
     def step():
         if n == 1:
@@ -176,6 +208,71 @@ def run_ours(args) -> dict:
         if n > 1:
             dist.barrier()
             torch.cuda.synchronize()
+
+    # ---- parity of the REAL multi-GPU kernels, checked where the driver can see it ------------------
+    # One eager step against NCCL's all-reduce / all-gather + an fp32 torch norm (vLLM's native
+    # definition, ir/ops/layernorm.py:39-58).  Tolerances: first fused call -- residual bit-exact
+    # at N=2 (one add, one rounding on both sides), <= 1e-2 relative otherwise (NCCL's summation
+    # order differs; north_star's bound); the whole chained step <= 1e-2 relative (Frobenius);
+    # the logits gather bit-exact.  A miss aborts the run with a non-zero exit.
+    def rel(a, b):
+        return float((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-30))
+
+    def ref_call(xi, res, g):
+        sref = xi.clone()
+        dist.all_reduce(sref)
+        x32 = sref.float() + res.float()
+        rnew = x32.to(torch.bfloat16)
+        y = (x32 * torch.rsqrt(x32.pow(2).mean(-1, keepdim=True) + eps)).to(torch.bfloat16) * g
+        return y, rnew
+
+    parity = None
+    if n > 1:
+        checks, worst = {}, 0.0
+        variants = [("auto", variant)]
+        if comm.nvls and variant != C.NVLS:
+            variants.append(("nvls", C.NVLS))
+        for vname, vcode in variants:
+            residual.copy_(res_host)
+            comm.all_reduce_add_rmsnorm_into(x[0], residual, gammas[0], eps, h, vcode)
+            y_ref, r_ref = ref_call(x[0], res_host.to(dev), gammas[0])
+            torch.cuda.synchronize()
+            e_r, e_y = rel(residual, r_ref), rel(h, y_ref)
+            ok = e_r <= 1e-2 and e_y <= 1e-2
+            if n == 2 and vcode != C.NVLS:
+                ok = ok and torch.equal(residual, r_ref)
+            checks[f"first_call_{vname}"] = ok
+            worst = max(worst, e_r, e_y)
+        # the whole step, chained through the residual stream, exactly as it is timed
+        residual.copy_(res_host)
+        step()
+        r_ref = res_host.to(dev)
+        for i in range(calls):
+            y_ref, r_ref = ref_call(x[i], r_ref, gammas[i])
+        gathered = torch.empty(n, B, V // n, dtype=torch.bfloat16, device=dev)
+        dist.all_gather_into_tensor(gathered, logits_local)
+        logits_ref = gathered.permute(1, 0, 2).reshape(B, V)
+        torch.cuda.synchronize()
+        e_r, e_y = rel(residual, r_ref), rel(h, y_ref)
+        checks["step_residual"] = e_r <= 1e-2
+        checks["step_norm_out"] = e_y <= 1e-2
+        checks["logits_gather_bit_exact"] = bool(torch.equal(logits_full, logits_ref))
+        worst = max(worst, e_r, e_y)
+        flag = torch.tensor([0 if all(checks.values()) else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        w = torch.tensor([worst], dtype=torch.float64, device=dev)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        parity = {"ok": int(flag.item()) == 0, "max_rel": round(float(w.item()), 6),
+                  "checks_rank0": checks,
+                  "against": "NCCL all_reduce / all_gather_into_tensor + fp32 torch norm, every rank"}
+        if not parity["ok"]:
+            log(f"[rank {rank}] PARITY FAILURE: {checks} max_rel {worst}")
+            dist.barrier()
+            if rank == 0:
+                real_print(json.dumps({"metric": METRIC, "n_gpus": n, "parity": parity,
+                                       "error": "parity check failed; nothing was timed"}))
+            raise SystemExit(3)
+        residual.copy_(res_host)
 
     # ---- device-resident measurement: the step as a CUDA graph --------------------------------
     stream = torch.cuda.Stream()
@@ -235,6 +332,56 @@ def run_ours(args) -> dict:
     h2d = x_host.numel() * 2 + res_host.numel() * 2 + (logits_host.numel() * 2 if n > 1 else 0)
     d2h = out_host.numel() * 2 + (logits_out_host.numel() * 2 if n > 1 else 0)
 
+    # ---- N>1: the numbers the north star is stated in ----------------------------------------------
+    # (a) the step split into its fused all-reduce calls and the logits gather, each as its own
+    # graph; (b) one fused call per regime -- [64, H] (latency) and [4096, H] (bandwidth) -- for
+    # every variant that applies, as bus GB/s = 2(N-1)/N * S / t against the measured link peak.
+    per_call_us = gather_us = None
+    regimes = []
+    if n > 1:
+        def graph_of(fn):
+            with torch.cuda.stream(stream):
+                fn()
+            sync_all()
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(stream):
+                with torch.cuda.graph(gph, stream=stream):
+                    fn()
+            sync_all()
+            return gph
+
+        def ar_only():
+            for i in range(calls):
+                comm.all_reduce_add_rmsnorm_into(x[i], residual, gammas[i], eps, h, variant)
+
+        k2 = max(5, min(args.steps, 20))
+        ms_ar, _ = timed_steps(graph_of(ar_only).replay, k2, 3)
+        ms_ag, _ = timed_steps(graph_of(lambda: comm.all_gather_lastdim(logits_local, out=logits_full)).replay, k2, 3)
+        per_call_us = round(ms_ar * 1e3 / calls, 3)
+        gather_us = round(ms_ag * 1e3, 3)
+    if extras:
+        reps = 8
+        for tokens in (B, big_tokens):
+            xb = torch.randn(tokens, H, generator=gen).bfloat16().to(dev)
+            rb = torch.randn(tokens, H, generator=g7).bfloat16().to(dev)
+            hb = torch.empty_like(xb)
+            Sb = tokens * H * 2
+            names = [("auto", C.AUTO), ("twoshot", C.TWOSHOT)]
+            if Sb * n <= 2 * comm.max_bytes and Sb <= (4 << 20):
+                names.append(("oneshot", C.ONESHOT))
+            if comm.nvls:
+                names.append(("nvls", C.NVLS))
+            for vname, vcode in names:
+                def rep(vcode=vcode):
+                    for _ in range(reps):
+                        comm.all_reduce_add_rmsnorm_into(xb, rb, gammas[0], eps, hb, vcode)
+                ms, _ = timed_steps(graph_of(rep).replay, 5, 3)
+                us = ms * 1e3 / reps
+                bus = 2 * (n - 1) / n * Sb / (us * 1e-6) / 1e9
+                regimes.append({"shape": [tokens, H], "bytes": Sb, "variant": vname, "us_per_call": round(us, 3),
+                                "bus_gbs": round(bus, 1), "frac": round(bus / NVLINK_PEAK_GBS, 4)})
+            del xb, rb, hb
+
     comm.check_health()
 
     # ---- roofline of the dominant kernel -----------------------------------------------------------
@@ -252,14 +399,19 @@ def run_ours(args) -> dict:
     else:
         bus_bytes = 2 * (n - 1) / n * S  # all-reduce bus bytes
         achieved = bus_bytes * calls / (ms_per_step * 1e-3) / 1e9
-        roof = {"bound": "nvlink", "kernel": "ar_norm_kernel<bf16>", "achieved": round(achieved, 2),
+        if per_call_us:  # the fused calls alone (the gather is timed separately)
+            achieved = bus_bytes / (per_call_us * 1e-6) / 1e9
+        roof = {"bound": "nvlink", "kernel": "ar_norm_kernel<bf16> / ar_norm_cluster_kernel<bf16> / nvls_kernel<bf16> (by size)",
+                "achieved": round(achieved, 2),
                 "peak": NVLINK_PEAK_GBS, "unit": "GB/s", "frac": round(achieved / NVLINK_PEAK_GBS, 4),
-                "traffic": None,
+                "traffic": None, "per_call_us": per_call_us, "gather_us": gather_us, "regimes": regimes,
                 "peak_source": "measured peer copy 770 GB/s per direction (B200_PROFILING.md); "
                                "nominal 900",
                 "algorithmic_bytes_per_launch": bus_bytes,
-                "note": "achieved counts the step's all-reduce bus bytes over the whole step time "
-                        "(the lm_head gather is inside the step)"}
+                "note": "achieved = bus bytes of one fused call / its time inside a graph of the step's "
+                        "fused calls alone; `regimes` = one fused call per size and variant, same process; "
+                        "with NVLS every byte crosses the link once, so bus GB/s (ring convention) can "
+                        "exceed the per-direction link peak"}
 
     result = {
         "metric": METRIC,
@@ -270,21 +422,13 @@ def run_ours(args) -> dict:
         "warmup": max(3, args.warmup),
         "ms_per_step": round(ms_per_step, 5),
         "higher_is_better": True,
-        "scaling": "weak",
+        "scaling": "fixed batch per step at every N (see DESIGN.md 6)",
         "vs_baseline": None,
         "dtype": "bf16",
         "data": "synthetic",
-        "config": {
-            "workload": f"{shp['model']} TP={n} decode hot path, batch {B}: {calls} x "
-                        + ("fused residual-add+RMSNorm" if n == 1 else
-                           "fused all-reduce+residual-add+RMSNorm + 1 lm_head all-gather")
-                        + f" on [{B},{H}] bf16",
-            "hidden": H, "layers": L, "vocab": V, "batch": B, "tp": n,
-            "calls_per_step": launches_per_step,
-            "l2": "256 MiB buffer rewritten between timed steps (untimed) to flush the 126 MB L2",
-            "execution": "step captured once as a CUDA graph, replayed per timed step",
-            "variant": args.variant,
-        },
+        "parity": parity,
+        "nvls": bool(getattr(comm, "nvls", False)),
+        "config": workload_config(shp, n, B, args.variant),
         "clocks": clocks,
         "e2e": {"value": round(B / (e2e_ms * 1e-3), 1), "unit": "tokens/s",
                 "ms_per_step": round(e2e_ms, 5), "steps": e2e_steps,
@@ -294,8 +438,8 @@ def run_ours(args) -> dict:
         "roofline": roof,
         "us_per_call": round(ms_per_step * 1e3 / launches_per_step, 3),
     }
-    if n == 1 and rank == 0 and not args.no_cpu_baseline:
-        result["cpu_baseline"] = cpu_baseline_port(shp, B, calls)
+    if rank == 0 and not args.no_cpu_baseline:
+        result["cpu_baseline"] = cpu_baseline_port(shp, B, calls, n, budget_s=10.0 if n == 1 else 5.0)
     if n > 1:
         dist.barrier()
         comm.close()
@@ -305,31 +449,37 @@ def run_ours(args) -> dict:
 
 # ================================ CPU baselines ==========================================================
 
-def cpu_baseline_port(shp: dict, B: int, calls: int, budget_s: float = 10.0) -> dict:
+def cpu_baseline_port(shp: dict, B: int, calls: int, n: int = 1, budget_s: float = 10.0) -> dict:
     """The oracle (a port of the reference's algorithm) timed on the host cores: the same
-    step, as many repetitions as fit in ~budget_s."""
+    step (all N ranks' all-reduce + residual + RMSNorm in one process at N > 1), as many
+    repetitions as fit in ~budget_s."""
     import torch
     from oracle import oracle
     H, eps = shp["hidden"], shp["eps"]
     cores = os.cpu_count() or 1
     oracle.set_num_threads(cores)
     g = torch.Generator().manual_seed(1)
-    xs = [torch.randn(B, H, generator=g).bfloat16() for _ in range(4)]
+    xs = [[torch.randn(B, H, generator=g).bfloat16() for _ in range(n)] for _ in range(4)]
     res = torch.randn(B, H, generator=g).bfloat16()
     gamma = torch.randn(H, generator=g).bfloat16()
     t0 = time.perf_counter()
     steps = 0
     while True:
         for i in range(calls):
-            _, res = oracle.fused_add_rms_norm(xs[i % 4], res, gamma, eps)
+            if n == 1:
+                _, res = oracle.fused_add_rms_norm(xs[i % 4][0], res, gamma, eps)
+            else:
+                _, res, _ = oracle.all_reduce_add_rms_norm(xs[i % 4], res, gamma, eps)
         steps += 1
         if time.perf_counter() - t0 > budget_s or steps >= 200:
             break
     dt = (time.perf_counter() - t0) / steps
+    what = "fused residual-add+RMSNorm" if n == 1 else f"{n}-rank all-reduce + residual-add+RMSNorm"
     return {"value": round(B / dt, 1), "unit": "tokens/s", "cores": oracle.num_threads(),
             "kind": "port", "ms_per_step": round(dt * 1e3, 3),
-            "sample": f"{steps} full steps ({calls} fused residual-add+RMSNorm calls on [{B},{H}] "
-                      f"bf16 each) of oracle/oracle.c with OpenMP"}
+            "sample": f"{steps} full steps ({calls} {what} calls on [{B},{H}] bf16 each"
+                      + ("" if n == 1 else ", logits gather not included")
+                      + ") of oracle/oracle.c with OpenMP"}
 
 
 def _ref_worker(rank, world, port, shp, B, calls, steps, warmup, use_vllm, q):
@@ -409,45 +559,83 @@ def _ref_worker(rank, world, port, shp, B, calls, steps, warmup, use_vllm, q):
     q.put((rank, dt, kind, threads))
 
 
+# Variables torch.distributed.run exports into its ranks.  The reference arm starts its OWN
+# gloo group from rank 0, so none of them may leak into the spawned workers: with
+# TORCHELASTIC_USE_AGENT_STORE=True every rank of a tcp:// rendezvous becomes a TCPStore
+# client and nobody serves (the round-1 hang at N>1).
+_TORCHRUN_ENV_PREFIXES = ("TORCHELASTIC_", "GROUP_", "ROLE_", "MASTER_", "TORCH_NCCL_", "PET_")
+_TORCHRUN_ENV_NAMES = ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "NODE_RANK",
+                       "OMP_NUM_THREADS")
+
+
+def _scrub_torchrun_env() -> None:
+    for k in list(os.environ):
+        if k in _TORCHRUN_ENV_NAMES or k.startswith(_TORCHRUN_ENV_PREFIXES):
+            del os.environ[k]
+
+
+def _free_port() -> int:
+    import socket
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        return sk.getsockname()[1]
+
+
 def run_reference(args) -> dict | None:
     """--impl reference: the reference's own CPU implementation of the path (vLLM's
     communicator API over gloo + its native fused_add_rms_norm) on the box's host cores.
     Under torchrun only rank 0 works; it spawns its own N gloo workers."""
     if int(os.environ.get("RANK", 0)) != 0:
         return None
+    _scrub_torchrun_env()
+    import queue as queue_mod
     import torch.multiprocessing as mp
     n = args.gpus
     shp = model_shape(n)
     B, calls = args.batch, 2 * shp["layers"] + 1
-    steps = max(1, min(args.steps, 10))
-    warmup = max(1, min(args.warmup, 2))
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29400 + (os.getpid() % 500)
+    port = _free_port()
     procs = [ctx.Process(target=_ref_worker,
                          args=(r, n, port, shp, B, calls, steps, warmup, not args.no_vllm, q))
              for r in range(n)]
     for p in procs:
         p.start()
-    outs = [q.get(timeout=1500) for _ in range(n)]
+    outs, deadline = [], time.time() + args.ref_timeout
+    while len(outs) < n:
+        try:
+            outs.append(q.get(timeout=1.0))
+            continue
+        except queue_mod.Empty:
+            pass
+        dead = [p for p in procs if p.exitcode not in (None, 0)]
+        if dead or time.time() > deadline:
+            for p in procs:
+                if p.is_alive():
+                    p.terminate()
+            why = (f"worker exited with code {dead[0].exitcode}" if dead
+                   else f"no result within {args.ref_timeout} s")
+            raise SystemExit(f"reference arm failed: {why}")
     for p in procs:
         p.join(timeout=60)
     dt = max(o[1] for o in outs)
     kind = outs[0][2]
     threads = outs[0][3]
     val = round(B / dt, 1)
-    sample = (f"{steps} full steps of the same workload, {n} gloo process(es) x {threads} threads")
+    sample = (f"{steps} full steps (after {warmup} warm-up) of the same workload, {n} gloo "
+              f"process(es) x {threads} threads")
     return {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": n,
         "steps": steps, "warmup": warmup, "ms_per_step": round(dt * 1e3, 3),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "higher_is_better": True, "scaling": "fixed batch per step at every N (see DESIGN.md 6)",
+        "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": f"{shp['model']} TP={n} decode hot path, batch {B} on host cores "
-                               f"(vLLM CPU/gloo path)", "hidden": shp["hidden"],
-                   "layers": shp["layers"], "vocab": shp["vocab"], "batch": B, "tp": n},
+        "config": workload_config(shp, n, B, args.variant),
         "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": threads * n,
                          "kind": "reference" if kind == "reference" else "port",
-                         "detail": kind, "sample": sample},
+                         "detail": kind + ": vLLM CPU/gloo communicator path on the host cores",
+                         "sample": sample},
         "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -460,19 +648,26 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "nvls"])
+    ap.add_argument("--no-extras", action="store_true",
+                    help="N>1: skip the per-regime table (1 MiB and 64 MiB fused calls, every variant)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-vllm", action="store_true", help="reference arm: skip vLLM, time the port")
+    ap.add_argument("--ref-timeout", type=float, default=1200.0,
+                    help="reference arm: give up if the gloo workers have not reported by then")
     args = ap.parse_args()
     # Libraries (NCCL's version banner, vLLM's logger) write to stdout; the contract is ONE JSON
     # line there.  Everything else is sent to stderr while the run is in progress.
+    global _REAL_STDOUT_FD
     sys.stdout.flush()
     real_stdout = os.dup(1)
+    _REAL_STDOUT_FD = real_stdout
     os.dup2(2, 1)
     try:
         res = run_reference(args) if args.impl == "reference" else run_ours(args)
     finally:
         sys.stdout.flush()
+        _REAL_STDOUT_FD = None
         os.dup2(real_stdout, 1)
         os.close(real_stdout)
     if res is not None:

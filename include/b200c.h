@@ -37,6 +37,8 @@ extern "C" {
 #define B200C_AUTO 0
 #define B200C_ONESHOT 1 /* every rank pushes its whole message to every peer */
 #define B200C_TWOSHOT 2 /* push-scatter, reduce own chunk, push-gather */
+#define B200C_NVLS 3    /* in-switch reduction (multimem.ld_reduce / multimem.st); needs b200c_attach_nvls; \
+                           tolerance-parity: the switch's summation order is unspecified */
 
 /* error codes */
 #define B200C_OK 0
@@ -56,6 +58,12 @@ extern "C" {
 #define B200C_TUNE_PDL 7               /* programmatic dependent launch on/off (default on) */
 #define B200C_TUNE_ONESHOT_SPLIT 8     /* CTAs (cluster size) per row, one-shot fused: 0 auto, 1 none */
 #define B200C_TUNE_DEBUG_EPOCH 9       /* test hook, host-synchronous: read / jump the call counter     */
+#define B200C_TUNE_TRAP_ON_TIMEOUT 10  /* 0 (default): a timed-out wait sets the sticky error word; 1: it also \
+                                          executes `trap`, so the next CUDA call of the process fails    */
+
+#define B200C_TUNE_NVLS_MIN_BYTES 11   /* AUTO picks NVLS at or above this size; < 0 (default) = never  */
+#define B200C_TUNE_NVLS_LINK_BLOCKS 12 /* NVLS CTAs doing copy-in + in-switch reduce; 0 = half the grid */
+#define B200C_TUNE_NVLS_GROUPS 13      /* NVLS copy-in pipeline groups (1..8); 0 = by size               */
 
 typedef struct b200c_ctx b200c_ctx;
 
@@ -103,13 +111,32 @@ int b200c_init(int rank, int world, void* const* arena_ptrs, size_t max_bytes, s
 /* Replaces dispose (VLLM/_custom_ops.py:2888-2889). Host-synchronous. */
 int b200c_destroy(b200c_ctx* ctx);
 
+/* ---- NVLS (NVSwitch multicast) buffer ----------------------------------------------
+ * The B200C_NVLS variant reduces inside the switch, which can only read and write a
+ * buffer that is bound to a multicast object on every rank.  The caller provides it
+ * (e.g. torch.distributed._symmetric_memory: empty + rendezvous gives both mappings):
+ * uc_ptr = this rank's copy through its ordinary mapping, mc_ptr = the multicast mapping
+ * of the same offset range, bytes >= b200c_nvls_bytes(max_bytes).  attach arms the
+ * rank's own copy (host-synchronous); run a host barrier across the group before the
+ * first NVLS call.  The ctx does not own the buffer.
+ * Replaces the symmetric-memory set-up of SymmMemCommunicator.__init__
+ * (VLLM/distributed/device_communicators/symm_mem.py:88-112) and the multicast
+ * workspace of FlashInfer's MNNVL all-reduce (FI/comm/trtllm_mnnvl_ar.py). */
+int b200c_nvls_bytes(size_t max_bytes, size_t* out_bytes);
+int b200c_attach_nvls(b200c_ctx* ctx, void* uc_ptr, void* mc_ptr, size_t bytes);
+
 int b200c_set_tuning(b200c_ctx* ctx, int key, long long value);
 int b200c_get_tuning(b200c_ctx* ctx, int key, long long* value);
 
 /* Host-synchronous read of the sticky device-side error word (0 = healthy,
- * B200C_ETIMEOUT if a wait on a peer timed out; results since then are garbage).
+ * B200C_ETIMEOUT if a wait on a peer timed out; results since then are garbage;
+ * B200C_ECUDA if the one-shot cluster kernel found itself running with a cluster
+ * shape other than the one it was compiled for and wrote nothing).
  * The reference's barrier spins forever on a dead peer
- * (vllm_custom_all_reduce.cuh:190-211); this library bounds the wait. */
+ * (vllm_custom_all_reduce.cuh:190-211); this library bounds the wait, and with
+ * B200C_TUNE_TRAP_ON_TIMEOUT it turns a timeout into a dead CUDA context -- the
+ * same "worker is gone" signal the reference launcher acts on
+ * (REF/src/launch.py:130-144, 386-388) -- instead of wrong results. */
 int b200c_query_error(b200c_ctx* ctx);
 
 /* ---- the hot path -----------------------------------------------------------------

@@ -30,8 +30,11 @@ def test_no_cuda_needed_for_metadata_calls():
     assert lib.b200c_version() == 1
     out = ctypes.c_size_t(0)
     assert lib.b200c_arena_bytes(8, 1 << 20, 1 << 20, 1 << 20, ctypes.byref(out)) == 0
-    # ctrl + 3 regions of 2*max + 2 ag + 8*2 mailboxes
-    assert out.value == 64 * 1024 + 6 * (1 << 20) + 2 * (1 << 20) + 16 * (1 << 20)
+    # ctrl + 3 regions of 2 halves (max + the 256-byte-aligned chunk-rounding slack) + 2 ag
+    # + 8*2 mailboxes
+    assert out.value == 64 * 1024 + 6 * ((1 << 20) + 256) + 2 * (1 << 20) + 16 * (1 << 20)
+    assert lib.b200c_nvls_bytes(1 << 20, ctypes.byref(out)) == 0
+    assert out.value == 16 * 1024 + 4 * ((1 << 20) + 256)  # flags + xin + 3 rotating sum regions
     assert lib.b200c_arena_bytes(9, 16, 16, 16, ctypes.byref(out)) == C.EINVAL
     assert b"world" in lib.b200c_last_error()
 
@@ -44,5 +47,6 @@ def test_header_constants_match_binding():
     for k in ("BF16", "F16", "F32", "AUTO", "ONESHOT", "TWOSHOT", "EINVAL", "ECUDA", "ETOOBIG",
               "ETIMEOUT", "ENOMEM", "TUNE_ONESHOT_MAX_BYTES", "TUNE_ONESHOT_BLOCKS",
               "TUNE_TWOSHOT_BLOCKS", "TUNE_SPIN_TIMEOUT_MS", "TUNE_COPY_BLOCKS", "TUNE_LINK_BLOCKS",
-              "TUNE_PDL", "TUNE_ONESHOT_SPLIT", "TUNE_DEBUG_EPOCH"):
+              "TUNE_PDL", "TUNE_ONESHOT_SPLIT", "TUNE_DEBUG_EPOCH", "NVLS", "TUNE_TRAP_ON_TIMEOUT",
+              "TUNE_NVLS_MIN_BYTES", "TUNE_NVLS_LINK_BLOCKS", "TUNE_NVLS_GROUPS"):
         assert int(consts[k]) == getattr(C, k), k

@@ -108,14 +108,24 @@ def _pp_worker(rank, world, port, q, tp, pp, golden):
         ppg.device_communicator = _FakeComm()   # route through the patched channel
         tpg = ps.get_tp_group() if tp > 1 else None
         hs, rs = oracle.from_bits(g["hidden_states_in"]), oracle.from_bits(g["residual_in"])
-        for step in range(3):  # several steps: the channel must stay in lock-step
+        paths = []
+        orig_send_meta = pp_channel.send_meta
+        pp_channel.send_meta = lambda grp, meta, dst: paths.append(orig_send_meta(grp, meta, dst))
+        # several steps: the channel must stay in lock-step.  Steps 0-2 change the metadata
+        # every time, steps 3-5 repeat it (the decode steady state), step 6 changes it again,
+        # and 20 more repeats wrap the 16-slot ring.
+        tags = [0, 1, 2, 99, 99, 99, 7] + [7] * 20
+        for step, tag in enumerate(tags):
             if ppg.rank_in_group == 0:
-                ppg.send_tensor_dict({"hidden_states": hs, "residual": rs, "step": step},
+                ppg.send_tensor_dict({"hidden_states": hs, "residual": rs, "step": tag},
                                      all_gather_group=tpg)
             else:
                 d = ppg.recv_tensor_dict(all_gather_group=tpg)
-                assert d["step"] == step
+                assert d["step"] == tag
                 got = {k: oracle.to_bits(v) for k, v in d.items() if isinstance(v, torch.Tensor)}
+        if ppg.rank_in_group == 0:
+            # only the first message of the pair pays the reference's pickled gloo handshake
+            assert paths == ["gloo", "shm", "shm", "shm", "shm-same", "shm-same", "shm"] + ["shm-same"] * 20, paths
         torch.distributed.barrier()
     q.put((rank, (ppg.rank_in_group, ps.get_tp_group().rank_in_group, got)))
     ps.destroy_model_parallel()

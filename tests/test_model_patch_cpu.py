@@ -20,6 +20,7 @@ class Norm:
         self.weight = torch.ones(8); self.variance_epsilon = 1e-5
         self.has_weight = True; self.variance_size_override = None if ok else 4
 class Layer:
+    forward = model_patch._layer_forward      # a class whose forward IS the patched one
     def __init__(self, ok=True, bias=None):
         self.self_attn = types.SimpleNamespace(o_proj=Lin(bias))
         self.mlp = types.SimpleNamespace(down_proj=Lin())
@@ -55,6 +56,42 @@ layers = [Layer(bias=torch.zeros(8)), Layer()]
 model_patch._configure_model(Model(layers, 0, 2))
 assert not getattr(layers[0], "_b200c_fused", False) and layers[1]._b200c_fused
 assert layers[1]._b200c_input_partial is False
+
+# a subclass layer with its OWN forward (Qwen3 / Mistral / Glm4 style) is never touched, and its
+# fused neighbours reduce around it
+class OwnForward(Layer):
+    def forward(self, *a, **k): raise AssertionError("not called")
+layers = [Layer(), OwnForward(), Layer(), Layer()]
+model_patch._configure_model(Model(layers, 0, 4))
+assert [getattr(l, "_b200c_fused", False) for l in layers] == [True, False, True, True]
+assert layers[1].self_attn.o_proj.reduce_results and layers[1].mlp.down_proj.reduce_results
+assert layers[0].mlp.down_proj.reduce_results and not layers[2]._b200c_input_partial
+# ... while a subclass that inherits the patched forward is fused like its parent
+class Inherits(Layer): pass
+layers = [Inherits(), Inherits()]
+model_patch._configure_model(Model(layers, 0, 2))
+assert all(l._b200c_fused for l in layers) and layers[1]._b200c_input_partial
+
+# EAGLE3 aux hidden states read hidden+residual after each layer: no fusion at all
+layers = [Layer(), Layer()]
+m = Model(layers, 0, 2); m.aux_hidden_state_layers = (1,)
+model_patch._configure_model(m)
+assert not any(getattr(l, "_b200c_fused", False) for l in layers)
+assert all(l.self_attn.o_proj.reduce_results and l.mlp.down_proj.reduce_results for l in layers)
+
+# all-or-nothing: a failure half way puts every flag back
+class Exploding(Lin):
+    def __setattr__(self, k, v):
+        if k == "reduce_results" and v is False and getattr(self, "armed", False): raise RuntimeError("boom")
+        object.__setattr__(self, k, v)
+layers = [Layer(), Layer(), Layer()]
+layers[2].self_attn.o_proj = Exploding(); layers[2].self_attn.o_proj.armed = True
+try:
+    model_patch._configure_model(Model(layers, 0, 3)); raise SystemExit("expected a failure")
+except RuntimeError:
+    pass
+assert not any(getattr(l, "_b200c_fused", False) for l in layers)
+assert all(l.self_attn.o_proj.reduce_results and l.mlp.down_proj.reduce_results for l in layers)
 
 # TP=1 or a foreign communicator: nothing is touched
 for bad in (types.SimpleNamespace(world_size=1, device_communicator=None, unique_name="tp:0"),

@@ -16,11 +16,12 @@ LIB_PATH = os.environ.get("B200C_LIB", os.path.join(HERE, "libb200c.so"))
 MAX_RANKS = 8
 IPC_HANDLE_BYTES = 64
 BF16, F16, F32 = 0, 1, 2
-AUTO, ONESHOT, TWOSHOT = 0, 1, 2
+AUTO, ONESHOT, TWOSHOT, NVLS = 0, 1, 2, 3
 OK, EINVAL, ECUDA, ETOOBIG, ETIMEOUT, ENOMEM = 0, -1, -2, -3, -4, -5
 TUNE_ONESHOT_MAX_BYTES, TUNE_ONESHOT_BLOCKS, TUNE_TWOSHOT_BLOCKS = 1, 2, 3
 TUNE_SPIN_TIMEOUT_MS, TUNE_COPY_BLOCKS = 4, 5
 TUNE_LINK_BLOCKS, TUNE_PDL, TUNE_ONESHOT_SPLIT, TUNE_DEBUG_EPOCH = 6, 7, 8, 9
+TUNE_TRAP_ON_TIMEOUT, TUNE_NVLS_MIN_BYTES, TUNE_NVLS_LINK_BLOCKS, TUNE_NVLS_GROUPS = 10, 11, 12, 13
 NOALLOC_MAX_BYTES = 64 * 1024
 
 Handle = c_ubyte * IPC_HANDLE_BYTES
@@ -37,6 +38,8 @@ SIGNATURES = {
     "b200c_free_shared": (c_int, [c_void_p]),
     "b200c_init": (c_int, [c_int, c_int, PtrArray, c_size_t, c_size_t, c_size_t, POINTER(c_void_p)]),
     "b200c_destroy": (c_int, [c_void_p]),
+    "b200c_nvls_bytes": (c_int, [c_size_t, POINTER(c_size_t)]),
+    "b200c_attach_nvls": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t]),
     "b200c_set_tuning": (c_int, [c_void_p, c_int, c_longlong]),
     "b200c_get_tuning": (c_int, [c_void_p, c_int, POINTER(c_longlong)]),
     "b200c_query_error": (c_int, [c_void_p]),

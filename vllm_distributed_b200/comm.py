@@ -51,6 +51,29 @@ def open_handle(handle: bytes) -> int:
     return ptr.value
 
 
+def assert_peer_access(cpu_group, device: torch.device) -> None:
+    """Every pair of the group's GPUs must be able to map each other's memory, or the first
+    push would fault.  The reference checks the same before it builds its IPC buffers
+    (vllm/distributed/device_communicators/custom_all_reduce.py:151-163) and then falls back to
+    NCCL; here the caller (B200Communicator) catches PeerAccessError and does the same."""
+    import torch.distributed as dist
+    if device.type != "cuda":
+        return
+    world = dist.get_world_size(cpu_group)
+    mine = device.index if device.index is not None else torch.cuda.current_device()
+    idx: list = [None] * world
+    dist.all_gather_object(idx, mine, group=cpu_group)
+    bad = [j for j in idx if j != mine and not torch.cuda.can_device_access_peer(mine, j)]
+    flags: list = [None] * world
+    dist.all_gather_object(flags, bad, group=cpu_group)
+    if any(flags):
+        raise PeerAccessError(f"no peer access between GPUs {[(idx[r], b) for r, b in enumerate(flags) if b]}")
+
+
+class PeerAccessError(RuntimeError):
+    pass
+
+
 # ---- standalone norm ops (TP=1 and the unfused path; no communicator state) ----------------
 
 def _rows(x: torch.Tensor) -> tuple[int, int]:
@@ -89,6 +112,8 @@ class B200Comm:
         self.max_bytes, self.ag_bytes, self.p2p_bytes = max_bytes, ag_bytes, p2p_bytes
         self._owned_arena = owned_arena
         self._opened = opened or []
+        self.nvls = False          # True once a multicast buffer is attached
+        self._nvls_buf = None      # keeps the symmetric allocation alive
         ctx = c_void_p(0)
         arr = C.ptr_array(arena_ptrs) if arena_ptrs else None
         with torch.cuda.device(device):
@@ -99,12 +124,16 @@ class B200Comm:
     @classmethod
     def from_process_group(cls, cpu_group, device: torch.device,
                            max_bytes: int = DEFAULT_MAX_BYTES, ag_bytes: int = DEFAULT_AG_BYTES,
-                           p2p_bytes: int = DEFAULT_P2P_BYTES) -> "B200Comm":
+                           p2p_bytes: int = DEFAULT_P2P_BYTES, device_group=None) -> "B200Comm":
+        """cpu_group: a gloo group (handle exchange, barriers).  device_group: the NCCL group of
+        the same ranks; when given (and B200C_NVLS != 0) a symmetric-memory buffer is
+        rendezvoused over it and, if the fabric offers multicast, attached for the NVLS variant."""
         import torch.distributed as dist
         rank = dist.get_rank(cpu_group)
         world = dist.get_world_size(cpu_group)
         if world == 1:
             return cls(0, 1, None, 0, 0, 0, device)
+        assert_peer_access(cpu_group, device)
         nbytes = arena_bytes(world, max_bytes, ag_bytes, p2p_bytes)
         with torch.cuda.device(device):
             mine, handle = alloc_shared(nbytes)
@@ -120,9 +149,48 @@ class B200Comm:
                     opened.append(p)
             comm = cls(rank, world, ptrs, max_bytes, ag_bytes, p2p_bytes, device,
                        owned_arena=mine, opened=opened)
+        if device_group is not None and os.environ.get("B200C_NVLS", "1") != "0":
+            comm.try_attach_nvls(cpu_group, device_group)
         # every arena must be armed before any rank pushes into it
         dist.barrier(group=cpu_group)
         return comm
+
+    def try_attach_nvls(self, cpu_group, device_group) -> bool:
+        """Allocate + rendezvous a symmetric buffer (torch plumbing) and hand its unicast and
+        multicast mappings to the library.  All-or-nothing across the group: if any rank has no
+        multicast pointer (no NVSwitch, driver without fabric support) nobody attaches."""
+        import torch.distributed as dist
+        need = c_size_t(0)
+        C.check(C.lib().b200c_nvls_bytes(self.max_bytes, byref(need)))
+        mc = uc = 0
+        buf = None
+        why = ""
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            name = device_group.group_name
+            try:
+                symm_mem.enable_symm_mem_for_group(name)
+            except Exception:  # noqa: BLE001 -- no-op or deprecated in newer torch
+                pass
+            with torch.cuda.device(self.device):
+                buf = symm_mem.empty(need.value, dtype=torch.uint8, device=self.device)
+                hdl = symm_mem.rendezvous(buf, name)
+            mc, uc = int(hdl.multicast_ptr), int(buf.data_ptr())
+        except Exception as e:  # noqa: BLE001 -- the NVLS variant is optional
+            why = f"{type(e).__name__}: {e}"
+        oks: list = [None] * self.world
+        dist.all_gather_object(oks, bool(mc), group=cpu_group)
+        if not all(oks):
+            self.nvls_reason = why or "no multicast pointer on some rank"
+            return False
+        with torch.cuda.device(self.device):
+            C.check(C.lib().b200c_attach_nvls(self.ctx, uc, mc, need.value))
+        self._nvls_buf = buf
+        self.nvls = True
+        v = os.environ.get("B200C_NVLS_MIN_BYTES")
+        if v is not None:
+            self.set_tuning(C.TUNE_NVLS_MIN_BYTES, int(v))
+        return True
 
     # ---- tuning ----
     def set_tuning(self, key: int, value: int) -> None:
@@ -138,6 +206,8 @@ class B200Comm:
 
     # ---- predicates the communicator uses to decide between this path and NCCL ----
     def can_all_reduce(self, x: torch.Tensor) -> bool:
+        # (every size up to max_bytes fits both variants for every group size: the arena
+        # regions carry the chunk-rounding slack, see make_geom in csrc/b200c.cu)
         nbytes = x.numel() * x.element_size()
         return (x.is_cuda and x.dtype in DTYPE_CODE and x.is_contiguous() and nbytes % 16 == 0
                 and 0 < nbytes <= self.max_bytes and x.data_ptr() % 16 == 0)
@@ -215,6 +285,8 @@ class B200Comm:
             with torch.cuda.device(self.device):
                 C.lib().b200c_destroy(self.ctx)
                 self.ctx = c_void_p(0)
+                self._nvls_buf = None
+                self.nvls = False
                 for p in self._opened:
                     C.lib().b200c_close_handle(p)
                 self._opened = []

@@ -17,7 +17,8 @@ from vllm.distributed.device_communicators.cuda_communicator import CudaCommunic
 from vllm.logger import init_logger
 
 from . import _cabi as C
-from .comm import (DEFAULT_AG_BYTES, DEFAULT_MAX_BYTES, DEFAULT_P2P_BYTES, B200Comm)
+from .comm import (DEFAULT_AG_BYTES, DEFAULT_MAX_BYTES, DEFAULT_P2P_BYTES, B200Comm,
+                   PeerAccessError)
 
 logger = init_logger("vllm.b200c.communicator")  # under vLLM's logging tree so INFO is shown
 
@@ -63,9 +64,25 @@ class B200Communicator(CudaCommunicator):
             sizes = dict(max_bytes=DEFAULT_MAX_BYTES, ag_bytes=DEFAULT_AG_BYTES, p2p_bytes=1 << 20)
         else:
             sizes = dict(max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=DEFAULT_P2P_BYTES)
-        self.b200 = B200Comm.from_process_group(cpu_group, self.device, **sizes)
-        logger.info("b200c: %s group of %d ranks on NVLink arenas (%s)", kind, self.world_size,
-                    ", ".join(f"{k}={v >> 20} MiB" for k, v in sizes.items()))
+        try:
+            self.b200 = B200Comm.from_process_group(
+                cpu_group, self.device, device_group=device_group if kind == "tp" else None, **sizes)
+        except PeerAccessError as e:
+            # same decision as the reference's custom all-reduce (custom_all_reduce.py:151-163):
+            # without full peer access the stock communicator serves the group
+            logger.warning("b200c: %s; group %s stays on the stock communicator", e, unique_name)
+            return
+        # A wait on a peer that never answers: the reference's barrier would hang forever
+        # (vllm_custom_all_reduce.cuh:190-211).  Here the wait is bounded by minutes, not seconds
+        # (one rank may legitimately be late: a JIT compile, a host stall, a long upstream PP
+        # stage), and when it does expire the kernel traps, so the worker dies loudly -- the
+        # launcher turns that into its fatal-disconnect path (/root/reference/src/launch.py:130-144)
+        # -- instead of serving tokens computed from garbage.
+        self.b200.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, int(os.environ.get("B200C_SPIN_TIMEOUT_MS", 300000)))
+        self.b200.set_tuning(C.TUNE_TRAP_ON_TIMEOUT, int(os.environ.get("B200C_TRAP_ON_TIMEOUT", 1)))
+        logger.info("b200c: %s group of %d ranks on NVLink arenas (%s)%s", kind, self.world_size,
+                    ", ".join(f"{k}={v >> 20} MiB" for k, v in sizes.items()),
+                    ", NVLS multicast attached" if self.b200.nvls else "")
 
     # ---- a1..a5: all-reduce -------------------------------------------------------------------
     def all_reduce(self, input_: torch.Tensor) -> torch.Tensor:
@@ -118,7 +135,11 @@ class B200Communicator(CudaCommunicator):
         if dst is None:
             dst = (self.rank_in_group + 1) % self.world_size
         b = self.b200
-        if b is not None and b.can_p2p(tensor):
+        if b is not None and tensor.is_cuda and (tensor.numel() * tensor.element_size()) % 16 == 0:
+            # the receiver decides by the byte count alone (it allocates an aligned tensor), so
+            # the sender must too: a strided or misaligned source is copied, not re-routed
+            if not tensor.is_contiguous() or tensor.data_ptr() % 16:
+                tensor = tensor.contiguous() if not tensor.is_contiguous() else tensor.clone()
             b.send(tensor, dst)
             return
         super().send(tensor, dst)

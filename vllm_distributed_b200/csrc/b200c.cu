@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "../../include/b200c.h"
@@ -35,10 +36,18 @@ int fail(int code, const char* fmt, ...) {
 
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// bytes of one receive half / NVLS region for messages of up to max_bytes (see make_geom)
+size_t region_half(size_t max_bytes) {
+  return align_up(std::max<size_t>(max_bytes, 16) + 16 * (kMaxRanks - 1), 256);
+}
+
 ArenaGeom make_geom(int world, size_t max_bytes, size_t ag_bytes, size_t p2p_bytes,
                     size_t* total) {
   ArenaGeom g;
-  const size_t half = align_up(std::max<size_t>(max_bytes, 16), 256);
+  // A two-shot call on `world` ranks rounds the message up to world equal chunks of whole
+  // 16-byte vectors, i.e. by at most (world-1)*16 bytes: the slack makes every message of up to
+  // max_bytes fit whatever the group size (3, 5, 6 and 7 ranks rarely divide it).
+  const size_t half = region_half(max_bytes);
   g.hi_off = half;
   g.lam_stride = 2 * half;
   g.ag_off = kCtrlBytes + 3 * g.lam_stride;
@@ -64,9 +73,17 @@ struct b200c_ctx {
   int twoshot_blocks = 148;
   int copy_blocks = 64;
   long long spin_timeout_ms = 10000;
+  int trap_on_timeout = 0;  // 0: sticky error word, 1: trap (kill the context) -- see SpinGuard
   int link_blocks = 0;  // two-shot CTAs doing link work; 0 = half of the grid
   int pdl = 1;          // programmatic dependent launch on the real (non-emulated) kernels
   int oneshot_split = 0;  // CTAs per row in the one-shot fused kernel: 0 auto, 1 = no cluster
+  // NVLS variant (b200c_attach_nvls): the symmetric buffer through its unicast and multicast mappings
+  char* nv_uc = nullptr;
+  char* nv_mc = nullptr;
+  size_t nv_half = 0;
+  long long nvls_min_bytes = -1;  // AUTO picks NVLS at or above this size; < 0 = never
+  int nvls_link_blocks = 0;       // 0 = half of the grid
+  int nvls_groups = 0;            // copy-in pipeline groups; 0 = by size
 };
 
 namespace {
@@ -90,6 +107,11 @@ void fill_rank_params(const b200c_ctx* c, RankParams& p) {
   p.rank = c->rank;
   p.world = c->world;
   p.timeout_ns = (unsigned long long)c->spin_timeout_ms * 1000000ull;
+  p.trap = c->trap_on_timeout;
+  p.nv_uc = c->nv_uc;
+  p.nv_mc = c->nv_mc;
+  p.nv_half = c->nv_half;
+  p.nv_groups = 1;
 }
 
 void fill_copy_params(const b200c_ctx* c, CopyParams& p) {
@@ -100,6 +122,7 @@ void fill_copy_params(const b200c_ctx* c, CopyParams& p) {
   p.rank = c->rank;
   p.world = c->world;
   p.timeout_ns = (unsigned long long)c->spin_timeout_ms * 1000000ull;
+  p.trap = c->trap_on_timeout;
 }
 
 // Every CTA of a collective kernel must be resident at once (CTAs wait on peers' CTAs).
@@ -216,7 +239,8 @@ void norm_shape(int hv, int* vpt, int* threads) {
 }
 
 int pick_variant(const b200c_ctx* c, size_t bytes, int variant) {
-  if (variant == B200C_ONESHOT || variant == B200C_TWOSHOT) return variant;
+  if (variant == B200C_ONESHOT || variant == B200C_TWOSHOT || variant == B200C_NVLS) return variant;
+  if (c->nv_mc && c->nvls_min_bytes >= 0 && (long long)bytes >= c->nvls_min_bytes) return B200C_NVLS;
   // AUTO: one-shot below the measured crossover, provided `world` copies fit one region
   const bool fits = bytes * (size_t)c->world <= c->geom.lam_stride;
   return ((long long)bytes <= c->oneshot_max_bytes && fits) ? B200C_ONESHOT : B200C_TWOSHOT;
@@ -233,6 +257,11 @@ int check_ar_fit(const b200c_ctx* c, size_t bytes, int variant) {
     const size_t nvec = bytes / 16, chunk = (nvec + c->world - 1) / c->world;
     if (chunk * 16 * c->world > c->geom.hi_off)
       return fail(B200C_ETOOBIG, "two-shot scatter area too small for %zu bytes", bytes);
+  }
+  if (variant == B200C_NVLS) {
+    if (!c->nv_mc)
+      return fail(B200C_EINVAL, "the NVLS variant needs a multicast buffer (b200c_attach_nvls)");
+    if (bytes > c->nv_half) return fail(B200C_ETOOBIG, "message of %zu bytes exceeds the NVLS regions", bytes);
   }
   return B200C_OK;
 }
@@ -281,37 +310,73 @@ int launch_ar_norm_v(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int
   return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
 }
 
-// one-shot fused, rows split over clusters of `split` CTAs
-template <typename T>
-int launch_ar_norm_cluster(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int split,
-                           int threads, int want_groups, cudaStream_t s) {
+// one-shot fused, rows split over clusters of SPLIT CTAs.  The cluster shape is compiled into
+// the kernel (__cluster_dims__), so no launch path can silently drop it; the launch attribute
+// is therefore NOT passed (the two must not disagree).
+template <typename T, int SPLIT>
+int launch_ar_norm_cluster_s(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int threads,
+                             int want_groups, cudaStream_t s) {
   if (nemu == 0) {
     int cap = 0;
-    int rc = coresident_clusters(ar_norm_cluster_kernel<T>, threads, split, ctxs[0]->sm_count, &cap);
+    int rc = coresident_clusters(ar_norm_cluster_kernel<T, SPLIT>, threads, SPLIT, ctxs[0]->sm_count, &cap);
     if (rc) return rc;
     const int g = std::max(1, std::min(want_groups, cap));
-    return launch(ar_norm_cluster_kernel<T>, dim3(g * split, 1, 1), threads, rp[0], s, false,
-                  ctxs[0]->pdl != 0, split);
+    return launch(ar_norm_cluster_kernel<T, SPLIT>, dim3(g * SPLIT, 1, 1), threads, rp[0], s, false,
+                  ctxs[0]->pdl != 0);
   }
   int cap = 0;
-  int rc = coresident_clusters(ar_norm_cluster_kernel_emu<T>, threads, split, ctxs[0]->sm_count, &cap);
+  int rc = coresident_clusters(ar_norm_cluster_kernel_emu<T, SPLIT>, threads, SPLIT, ctxs[0]->sm_count, &cap);
   if (rc) return rc;
   const int g = std::max(1, std::min(want_groups, cap / nemu));
   EmuParams ep;
   memset(&ep, 0, sizeof(ep));
   for (int r = 0; r < nemu; ++r) ep.r[r] = rp[r];
-  // Cooperative launch guarantees co-residency of the emulated ranks; if the driver refuses
-  // to combine it with cluster dimensions, launch plainly (the grid was sized to fit).
-  cudaLaunchConfig_t probe;
-  (void)probe;
-  int lrc = launch(ar_norm_cluster_kernel_emu<T>, dim3(g * split, nemu, 1), threads, ep, s, true,
-                   false, split);
-  if (lrc != B200C_OK) {
-    cudaGetLastError();
-    lrc = launch(ar_norm_cluster_kernel_emu<T>, dim3(g * split, nemu, 1), threads, ep, s, false,
-                 false, split);
+  // all emulated ranks wait on each other inside ONE launch: cooperative = guaranteed co-residency
+  return launch(ar_norm_cluster_kernel_emu<T, SPLIT>, dim3(g * SPLIT, nemu, 1), threads, ep, s, true);
+}
+
+template <typename T>
+int launch_ar_norm_cluster(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int split,
+                           int threads, int want_groups, cudaStream_t s) {
+  switch (split) {
+    case 1: return launch_ar_norm_cluster_s<T, 1>(ctxs, nemu, rp, threads, want_groups, s);
+    case 2: return launch_ar_norm_cluster_s<T, 2>(ctxs, nemu, rp, threads, want_groups, s);
+    case 4: return launch_ar_norm_cluster_s<T, 4>(ctxs, nemu, rp, threads, want_groups, s);
+    case 8: return launch_ar_norm_cluster_s<T, 8>(ctxs, nemu, rp, threads, want_groups, s);
   }
-  return lrc;
+  return fail(B200C_EINVAL, "cluster split %d is not one of 1, 2, 4, 8", split);
+}
+
+// ---- NVLS variant (real ranks only: a multicast group has one member per device) -------------
+int nvls_groups_for(const b200c_ctx* c, size_t bytes) {
+  if (c->nvls_groups > 0) return std::min(c->nvls_groups, kNvMaxGroups);
+  // one group below 4 MiB (the flag round trip costs more than the copy-in it would hide);
+  // above, about 1 MiB of the message per group
+  int g = (int)std::min<size_t>(kNvMaxGroups, bytes >> 20);
+  return bytes < (size_t)(4u << 20) ? 1 : std::max(1, g);
+}
+
+template <typename K>
+int launch_nvls_k(K kernel, b200c_ctx* c, RankParams p, size_t bytes, cudaStream_t s) {
+  const int threads = 512;
+  int cap = 0;
+  int rc = coresident_blocks(kernel, threads, c->sm_count, &cap);
+  if (rc) return rc;
+  const int g = std::max(2, std::min(twoshot_grid(c, bytes), cap));
+  const int l = c->nvls_link_blocks > 0 ? c->nvls_link_blocks : g / 2;
+  p.link_blocks = std::max(1, std::min(l, g - 1));
+  p.nv_groups = nvls_groups_for(c, bytes);
+  return launch(kernel, dim3(g, 1, 1), threads, p, s, false, c->pdl != 0);
+}
+
+template <typename T>
+int launch_nvls_norm(b200c_ctx* c, const RankParams& p, int vpt, size_t bytes, cudaStream_t s) {
+  switch (vpt) {
+    case 1: return launch_nvls_k(nvls_kernel<T, 1, true>, c, p, bytes, s);
+    case 2: return launch_nvls_k(nvls_kernel<T, 2, true>, c, p, bytes, s);
+    case 4: return launch_nvls_k(nvls_kernel<T, 4, true>, c, p, bytes, s);
+  }
+  return fail(B200C_EINVAL, "unsupported vectors-per-thread %d", vpt);
 }
 
 template <typename T, bool TWOSHOT>
@@ -432,18 +497,31 @@ int ar_norm_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins,
   if (rc) return rc;
   int vpt, threads;
   norm_shape(hv, &vpt, &threads);
+  if (variant == B200C_NVLS) {
+    if (nemu) return fail(B200C_EINVAL, "the NVLS variant cannot be emulated on one GPU");
+    // the row CTAs run 512 threads here (one launch shape for link and row work)
+    int v = 1;
+    while (v < 4 && (hv + v - 1) / v > 512) v *= 2;
+    switch (dtype) {
+      case B200C_BF16: return launch_nvls_norm<__nv_bfloat16>(c0, rp[0], v, bytes, s);
+      case B200C_F16: return launch_nvls_norm<__half>(c0, rp[0], v, bytes, s);
+      case B200C_F32: return launch_nvls_norm<float>(c0, rp[0], v, bytes, s);
+    }
+  }
   const bool two = variant == B200C_TWOSHOT;
   if (!two && c0->oneshot_split != 1) {
     // latency regime: one vector per thread, a row spread over up to 8 CTAs of a cluster
-    int split = c0->oneshot_split > 1 ? c0->oneshot_split : (hv + 127) / 128;
-    split = std::max(1, std::min(split, 8));
+    // (compiled shapes: 1, 2, 4, 8 CTAs per row)
+    int split = 1;
+    const int want_split = c0->oneshot_split > 1 ? c0->oneshot_split : (hv + 127) / 128;
+    while (split < 8 && split < want_split) split <<= 1;
     if (c0->oneshot_split == 0) {
       // splitting pays while all tokens x split CTAs are resident at once (about 2 per SM);
       // beyond that one wider CTA per row is faster (measured, tools/sweep.py)
       while (split > 1 && (long long)tokens * split > 2LL * c0->sm_count) split >>= 1;
     }
-    while (split > 1 && (hv + split - 1) / split > 256) ++split;
-    if (split <= 8 && (hv + split - 1) / split <= 256) {
+    while (split < 8 && (hv + split - 1) / split > 256) split <<= 1;
+    if ((hv + split - 1) / split <= 256) {
       const int cthreads = std::max(32, ((hv + split - 1) / split + 31) / 32 * 32);
       const int want_groups = std::min(tokens, c0->oneshot_blocks);
       switch (dtype) {
@@ -488,6 +566,14 @@ int ar_impl(b200c_ctx* const* ctxs, int nemu, const void* const* ins, void* cons
   variant = pick_variant(c0, bytes, variant);
   int rc = check_ar_fit(c0, bytes, variant);
   if (rc) return rc;
+  if (variant == B200C_NVLS) {
+    if (nemu) return fail(B200C_EINVAL, "the NVLS variant cannot be emulated on one GPU");
+    switch (dtype) {
+      case B200C_BF16: return launch_nvls_k(nvls_kernel<__nv_bfloat16, 1, false>, c0, rp[0], bytes, s);
+      case B200C_F16: return launch_nvls_k(nvls_kernel<__half, 1, false>, c0, rp[0], bytes, s);
+      case B200C_F32: return launch_nvls_k(nvls_kernel<float, 1, false>, c0, rp[0], bytes, s);
+    }
+  }
   const bool two = variant == B200C_TWOSHOT;
   const size_t nvec = bytes / 16;
   int want = two ? twoshot_grid(c0, bytes) : c0->oneshot_blocks;
@@ -642,6 +728,34 @@ int b200c_destroy(b200c_ctx* c) {
   return B200C_OK;
 }
 
+int b200c_nvls_bytes(size_t max_bytes, size_t* out_bytes) {
+  if (!out_bytes) return fail(B200C_EINVAL, "out_bytes is NULL");
+  *out_bytes = kNvCtrlBytes + 4 * region_half(max_bytes);
+  return B200C_OK;
+}
+
+int b200c_attach_nvls(b200c_ctx* c, void* uc_ptr, void* mc_ptr, size_t bytes) {
+  if (!c) return fail(B200C_EINVAL, "ctx is NULL");
+  if (c->world < 2 || !c->st) return fail(B200C_EINVAL, "NVLS needs a group of at least 2 ranks");
+  if (!uc_ptr || !mc_ptr || !aligned16(uc_ptr) || !aligned16(mc_ptr))
+    return fail(B200C_EINVAL, "NULL or misaligned NVLS buffer");
+  const size_t half = region_half(c->max_bytes);
+  if (bytes < kNvCtrlBytes + 4 * half)
+    return fail(B200C_ETOOBIG, "NVLS buffer of %zu bytes is smaller than the %zu this ctx needs", bytes,
+                kNvCtrlBytes + 4 * half);
+  char* uc = static_cast<char*>(uc_ptr);
+  // own copy: flags to zero, sum regions to "not arrived" (through the unicast mapping only)
+  CUDA_TRY(cudaMemset(uc, 0, kNvCtrlBytes));
+  fill_not_arrived_kernel<<<c->sm_count * 4, 256>>>(reinterpret_cast<uint4*>(uc + kNvCtrlBytes + half),
+                                                   3 * half / 16);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaDeviceSynchronize());
+  c->nv_uc = uc;
+  c->nv_mc = static_cast<char*>(mc_ptr);
+  c->nv_half = half;
+  return B200C_OK;
+}
+
 int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
   if (!c) return fail(B200C_EINVAL, "ctx is NULL");
   switch (key) {
@@ -653,6 +767,10 @@ int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
     case B200C_TUNE_LINK_BLOCKS: c->link_blocks = (int)std::max<long long>(0, v); break;
     case B200C_TUNE_PDL: c->pdl = v != 0; break;
     case B200C_TUNE_ONESHOT_SPLIT: c->oneshot_split = (int)std::max<long long>(0, std::min<long long>(8, v)); break;
+    case B200C_TUNE_TRAP_ON_TIMEOUT: c->trap_on_timeout = v != 0; break;
+    case B200C_TUNE_NVLS_MIN_BYTES: c->nvls_min_bytes = v; break;
+    case B200C_TUNE_NVLS_LINK_BLOCKS: c->nvls_link_blocks = (int)std::max<long long>(0, v); break;
+    case B200C_TUNE_NVLS_GROUPS: c->nvls_groups = (int)std::max<long long>(0, std::min<long long>(kNvMaxGroups, v)); break;
     case B200C_TUNE_DEBUG_EPOCH: {
       // test hook (host-synchronous): jump the all-reduce call counter, e.g. to just below 2^32
       if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
@@ -677,6 +795,10 @@ int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
     case B200C_TUNE_LINK_BLOCKS: *v = c->link_blocks; break;
     case B200C_TUNE_PDL: *v = c->pdl; break;
     case B200C_TUNE_ONESHOT_SPLIT: *v = c->oneshot_split; break;
+    case B200C_TUNE_TRAP_ON_TIMEOUT: *v = c->trap_on_timeout; break;
+    case B200C_TUNE_NVLS_MIN_BYTES: *v = c->nvls_min_bytes; break;
+    case B200C_TUNE_NVLS_LINK_BLOCKS: *v = c->nvls_link_blocks; break;
+    case B200C_TUNE_NVLS_GROUPS: *v = c->nvls_groups; break;
     case B200C_TUNE_DEBUG_EPOCH: {
       if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
       unsigned long long w = 0;
@@ -695,6 +817,9 @@ int b200c_query_error(b200c_ctx* c) {
   if (!c->st) return B200C_OK;
   uint32_t e = 0;
   CUDA_TRY(cudaMemcpy(&e, &c->st->error, sizeof(e), cudaMemcpyDeviceToHost));
+  if (e == kErrClusterShape)
+    return fail(B200C_ECUDA, "the one-shot cluster kernel ran with a cluster shape other than the "
+                "one it was compiled for (rank %d); its output was not written", c->rank);
   if (e) return fail(B200C_ETIMEOUT, "a device-side wait on a peer timed out (rank %d)", c->rank);
   return B200C_OK;
 }
@@ -960,7 +1085,7 @@ int b200c_emu_sendrecv(b200c_ctx* const* ctxs, int world, int src, int dst, cons
 namespace {
 
 constexpr size_t kNoAllocMaxBytes = 64 * 1024;
-constexpr size_t kNoAllocHalf = kNoAllocMaxBytes;                    // already 256-aligned
+constexpr size_t kNoAllocHalf = kNoAllocMaxBytes + 256;  // make_geom's half for this max_bytes (chunk-rounding slack)
 constexpr size_t kNoAllocArenaBytes = kCtrlBytes + 3 * 2 * kNoAllocHalf + 2 * 256 + kMaxRanks * 2 * 256;
 constexpr size_t kNoAllocStateStride = 256;
 static_assert(sizeof(LocalState) <= kNoAllocStateStride, "LocalState must fit its slot");
@@ -982,12 +1107,14 @@ struct NoAllocDevice {
   int sm_count = 0;
 };
 NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+std::mutex g_noalloc_mutex;  // first calls from several threads must not race on the table
 
 // Once per device, with that device current.
 int noalloc_setup(int* dev_out, NoAllocDevice** out) {
   int dev = 0;
   CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(B200C_EINVAL, "device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
   NoAllocDevice& d = g_noalloc_dev[dev];
   if (d.base == nullptr) {
     void* p = nullptr;

@@ -76,6 +76,19 @@ __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
   return v;
 }
 
+// ---- NVLS (NVSwitch multicast) ------------------------------------------------------------------
+// `mc` addresses come from a multicast mapping of a buffer that exists on every rank: a store
+// to one lands in every rank's copy (the switch replicates it), a ld_reduce returns the sum of
+// every rank's copy, added inside the switch (SASS: LDGMC.*ADD, STG on a multicast address).
+__device__ __forceinline__ void mc_st_v4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_st_release_u32(void* mc, uint32_t v) {
+  asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -135,22 +148,35 @@ __device__ __forceinline__ void scrub(uint4& v) {
 
 // ---- bounded waiting ----------------------------------------------------------------------------
 // A wait on a peer never spins forever: after timeout_ns (0 = unbounded) the sticky error
-// word is set and every later wait in this and following kernels falls through at once.
+// word is set.  What happens next is the caller's policy (`trap` in the kernel parameters):
+//   trap == 0  every later wait in this and following kernels falls through at once; results
+//              are garbage from then on and the host must poll b200c_query_error();
+//   trap != 0  the kernel executes `trap`: the CUDA context is dead, the next CUDA call of the
+//              process fails, and the serving loop sees a crashed worker instead of wrong tokens.
+constexpr uint32_t kErrTimeout = 1u;
+constexpr uint32_t kErrClusterShape = 2u;
+
 struct SpinGuard {
   uint32_t iters = 0;
   unsigned long long t0 = 0;
-  // returns true when the caller must give up
-  __device__ __forceinline__ bool expired(unsigned long long timeout_ns, uint32_t* err) {
+  // returns true when the caller must give up; P is RankParams or CopyParams
+  template <typename P>
+  __device__ __forceinline__ bool expired(const P& p) {
     if ((++iters & 0x3ffu) != 0) return false;
+    uint32_t* err = &p.st->error;
     if (ld_volatile_u32(err) != 0) return true;
-    if (timeout_ns == 0) return false;
+    if (p.timeout_ns == 0) return false;
     unsigned long long now = globaltimer_ns();
     if (t0 == 0) {
       t0 = now;
       return false;
     }
-    if (now - t0 > timeout_ns) {
-      atomicExch(err, 1u);
+    if (now - t0 > p.timeout_ns) {
+      atomicExch(err, kErrTimeout);
+      if (p.trap) {
+        __threadfence_system();
+        asm volatile("trap;");
+      }
       return true;
     }
     return false;
@@ -186,6 +212,15 @@ struct VecOps<__nv_bfloat16> {
   static __device__ __forceinline__ float round_trip(float x) {
     return __bfloat162float(__float2bfloat16_rn(x));
   }
+  // in-switch sum over all ranks of one 16-byte vector, fp32 accumulation, one rounding
+  static __device__ __forceinline__ uint4 mc_ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+  }
 };
 
 template <>
@@ -212,6 +247,14 @@ struct VecOps<__half> {
   static __device__ __forceinline__ float round_trip(float x) {
     return __half2float(__float2half_rn(x));
   }
+  static __device__ __forceinline__ uint4 mc_ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+  }
 };
 
 template <>
@@ -228,6 +271,14 @@ struct VecOps<float> {
                       __float_as_uint(f[3]));
   }
   static __device__ __forceinline__ float round_trip(float x) { return x; }
+  static __device__ __forceinline__ uint4 mc_ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+  }
 };
 
 // ---- block-wide sum (warp shuffles, one shared-memory hop) -------------------------------------

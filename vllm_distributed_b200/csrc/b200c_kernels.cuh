@@ -41,6 +41,10 @@ struct LocalState {
   unsigned long long dirty_hi[3];
   uint32_t send_seq[kMaxRanks];
   uint32_t recv_seq[kMaxRanks];
+  // NVLS variant: CTA arrival counters of the copy-in groups, and the bytes the switch wrote
+  // into each rotating sum region of the NVLS buffer (0 after a call of another variant)
+  uint32_t nv_arrive[8];
+  unsigned long long nv_dirty[3];
 };
 
 struct RankParams {
@@ -60,7 +64,14 @@ struct RankParams {
   int hidden;              // elements per row
   unsigned long long nvec;  // total 16-byte vectors
   unsigned long long timeout_ns;
+  int trap;         // policy when a wait times out (see SpinGuard)
   int link_blocks;  // two-shot: CTAs [0, link_blocks) do the link work, the rest the rows
+  // NVLS variant (see nvls_body): this rank's symmetric buffer through its own (unicast)
+  // mapping and through the multicast mapping, bytes per region, pipeline groups
+  char* nv_uc;
+  char* nv_mc;
+  size_t nv_half;
+  int nv_groups;
 };
 
 struct EmuParams {
@@ -77,7 +88,7 @@ __device__ __forceinline__ char* lam_region(const RankParams& p, int rank, uint3
 __device__ __forceinline__ uint4 wait_one(const char* addr, const RankParams& p, SpinGuard& sg) {
   uint4 v = ld_poll_v4(addr);
   while (not_arrived(v)) {
-    if (sg.expired(p.timeout_ns, &p.st->error)) break;
+    if (sg.expired(p)) break;
     v = ld_poll_v4(addr);
   }
   return v;
@@ -112,7 +123,7 @@ __device__ __forceinline__ uint4 gather_sum(const char* my_lo, size_t slot_bytes
           const int r = r0 + k;
           if (r < p.world && r != p.rank) pending |= not_arrived(v[k]);
         }
-        if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
+        if (pending && sg.expired(p)) break;
       } while (pending);
 #pragma unroll
       for (int k = 0; k < BATCH; ++k) {
@@ -142,6 +153,33 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
   for (size_t i = gtid; i < n; i += gsize) st_v4(base + i * 16, m);
 }
 
+
+// ---- NVLS buffer layout (bytes from its base; identical on every rank) ---------------------------
+// [0, 16K)       flags [8 groups][8 src], one per 128-byte line: flag[g][r] = epoch+1 of the last
+//                call whose copy-in group g rank r has completed (written through the multicast
+//                mapping, so one store updates every rank's copy)
+// 1 x nv_half    xin: this rank's input, copied in so that the switch can read it
+// 3 x nv_half    rotating sum regions, region = epoch % 3, armed with "not arrived"
+constexpr size_t kNvCtrlBytes = 16 * 1024;
+constexpr int kNvMaxGroups = 8;
+
+__device__ __forceinline__ char* nv_sum_region(char* base, const RankParams& p, uint32_t b) {
+  return base + kNvCtrlBytes + (size_t)(1u + b) * p.nv_half;
+}
+__device__ __forceinline__ char* nv_flag(char* base, int group, int src) {
+  return base + ((size_t)group * kMaxRanks + src) * kFlagStride;
+}
+
+// Re-arm everything the previous call dirtied: its arena region (push variants) and its sum
+// region in the NVLS buffer (NVLS variant); at most one of the extents is non-zero.
+__device__ __forceinline__ void rearm_previous(const RankParams& p, uint32_t pb, size_t tid,
+                                               size_t nthreads) {
+  char* prev = lam_region(p, p.rank, pb);
+  rearm(prev, p.st->dirty_lo[pb], tid, nthreads);
+  rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], tid, nthreads);
+  if (p.nv_uc != nullptr) rearm(nv_sum_region(p.nv_uc, p, pb), p.st->nv_dirty[pb], tid, nthreads);
+}
+
 // Call bookkeeping without an end-of-kernel rendezvous and without a fence: the epoch (high
 // half) and the tickets of the running call (low half) share one 64-bit word.  A CTA reads the
 // epoch, and only when all its threads have it does thread 0 take a ticket.  The CTA holding the
@@ -153,7 +191,7 @@ struct CallState {
   uint32_t ticket;  // meaningful in thread 0 only
 };
 
-__device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* /*unused*/) {
+__device__ __forceinline__ CallState begin_call(const RankParams& p) {
   // Every thread reads the epoch itself (one L2 hit, no shared-memory broadcast) and consumes
   // the value before the barrier, so when thread 0 takes the CTA's ticket afterwards every
   // thread of the CTA has finished reading it.  The ticket's own latency is off the critical
@@ -170,11 +208,13 @@ __device__ __forceinline__ CallState begin_call(const RankParams& p, uint32_t* /
 }
 
 __device__ __forceinline__ void end_call(const RankParams& p, const CallState& cs,
-                                         unsigned long long dlo, unsigned long long dhi) {
+                                         unsigned long long dlo, unsigned long long dhi,
+                                         unsigned long long dnv = 0ull) {
   if (threadIdx.x == 0 && cs.ticket == gridDim.x - 1) {
     const uint32_t b = cs.epoch % 3u;
     p.st->dirty_lo[b] = dlo;
     p.st->dirty_hi[b] = dhi;
+    p.st->nv_dirty[b] = dnv;
     // 0xffffffff is a multiple of 3: wrapping from 0xfffffffe straight to 0 keeps the region
     // sequence ... 1, 2, 0 ... intact after 2^32 calls (about a week of 70B decode)
     const uint32_t next = (cs.epoch + 1u == 0xffffffffu) ? 0u : cs.epoch + 1u;
@@ -316,7 +356,7 @@ __device__ __forceinline__ void reduce_gather_range(const RankParams& p, uint32_
           }
         }
       }
-      if (pending && sg.expired(p.timeout_ns, &p.st->error)) break;
+      if (pending && sg.expired(p)) break;
     } while (pending);
 #pragma unroll
     for (int u = 0; u < UB; ++u) {
@@ -460,7 +500,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   load_gamma<T, VPT>(gam, p);  // weights: safe to read before the previous kernel has finished
   pdl_wait();
 
-  const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
+  const CallState cs = begin_call(p);
   const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t nvec = (size_t)p.nvec;
@@ -503,11 +543,7 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   }
 
   // ---- re-arm the previous call's region while the pushes are in flight
-  if (is_row) {
-    char* prev = lam_region(p, p.rank, pb);
-    rearm(prev, p.st->dirty_lo[pb], rtid, rsize);
-    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], rtid, rsize);
-  }
+  if (is_row) rearm_previous(p, pb, rtid, rsize);
 
   // ---- two-shot: reduce my chunk, push the sums to every rank's hi half
   if (TWOSHOT && is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
@@ -545,13 +581,24 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
 // cluster, one vector per thread, so the (N-1) pushes and polls of a row are spread over P SMs
 // and all in flight at once.  The row's sum of squares is combined through distributed shared
 // memory in fixed CTA order (same bits on every rank).  P == 1 degenerates to one CTA per row.
-template <typename T>
+//
+// P is a COMPILE-TIME property of the kernel (__cluster_dims__), not a launch attribute: a
+// launch path that drops launch attributes (ncu re-issuing a cooperative launch did exactly
+// that in round 1: launch__cluster_dim_x = 0, every CTA its own cluster, 3/4 of each row never
+// written) cannot change the shape the indexing below relies on.  The shape is checked on the
+// device as well; a mismatch sets the sticky error word to kErrClusterShape and does nothing.
+template <typename T, int SPLIT>
 __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float* smem,
                                                      float (*part)[kMaxRanks] /* [2][8] */) {
   constexpr int EPV = VecOps<T>::EPV;
+  constexpr uint32_t P = SPLIT;
   pdl_launch_dependents();
-  const uint32_t P = cluster_nctarank();
-  const uint32_t cta = cluster_ctarank();
+  if (cluster_nctarank() != P) {  // uniform over the grid: every CTA leaves, nobody waits
+    pdl_wait();
+    if (threadIdx.x == 0) atomicExch(&p.st->error, kErrClusterShape);
+    return;
+  }
+  const uint32_t cta = (P > 1) ? cluster_ctarank() : 0u;
   const int c = (int)(cta * blockDim.x + threadIdx.x);  // vector index inside the row
   const bool valid = c < p.hv;
   uint4 gam = make_uint4(0, 0, 0, 0);
@@ -563,7 +610,7 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
   uint4 v0 = make_uint4(0, 0, 0, 0);
   if (valid && group < p.tokens)
     v0 = ld_stream_v4((const char*)p.in + ((size_t)group * p.hv + c) * 16);
-  const CallState cs = begin_call(p, reinterpret_cast<uint32_t*>(smem + 64));
+  const CallState cs = begin_call(p);
   const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t nvec = (size_t)p.nvec;
@@ -586,11 +633,7 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
         if (r < p.world && r != p.rank) st_push_v4(lam_region(p, r, b) + slot_off + idx * 16, v);
     }
   }
-  {
-    char* prev = lam_region(p, p.rank, pb);
-    rearm(prev, p.st->dirty_lo[pb], gtid, gsize);
-    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], gtid, gsize);
-  }
+  rearm_previous(p, pb, gtid, gsize);
   // every CTA of the cluster must be running before its shared memory is written remotely;
   // this wait overlaps the fabric flight time of the pushes
   if (P > 1) cluster_sync_all();
@@ -625,6 +668,7 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
       if (threadIdx.x < P) st_dsmem_f32(&part[pp][cta], threadIdx.x, total);
       cluster_sync_all();
       total = 0.0f;
+#pragma unroll
       for (uint32_t q = 0; q < P; ++q) total += part[pp][q];
       pp ^= 1;
     }
@@ -640,28 +684,28 @@ __device__ __forceinline__ void ar_norm_cluster_body(const RankParams& p, float*
   end_call(p, cs, (unsigned long long)p.world * nvec * 16, 0ull);
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256) ar_norm_cluster_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+template <typename T, int SPLIT>
+__global__ void __cluster_dims__(SPLIT, 1, 1) __launch_bounds__(256)
+    ar_norm_cluster_kernel(const __grid_constant__ RankParams p) {
+  __shared__ float smem[64];  // 2 x 32 reduction banks
   __shared__ float part[2][kMaxRanks];
-  ar_norm_cluster_body<T>(p, smem, part);
+  ar_norm_cluster_body<T, SPLIT>(p, smem, part);
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256)
+template <typename T, int SPLIT>
+__global__ void __cluster_dims__(SPLIT, 1, 1) __launch_bounds__(256)
     ar_norm_cluster_kernel_emu(const __grid_constant__ EmuParams ep) {
-  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float smem[64];  // 2 x 32 reduction banks
   __shared__ float part[2][kMaxRanks];
-  ar_norm_cluster_body<T>(ep.r[blockIdx.y], smem, part);
+  ar_norm_cluster_body<T, SPLIT>(ep.r[blockIdx.y], smem, part);
 }
 
 // ---- plain all-reduce (no epilogue): flat vector indexing -----------------------------------------
 template <typename T, bool TWOSHOT>
 __device__ __forceinline__ void ar_body(const RankParams& p) {
-  __shared__ uint32_t s_epoch;
   pdl_launch_dependents();
   pdl_wait();
-  const CallState cs = begin_call(p, &s_epoch);
+  const CallState cs = begin_call(p);
   const uint32_t epoch = cs.epoch;
   const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;  // from b: epoch + 2 may overflow
   const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -693,11 +737,7 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
   } else if (is_link) {
     scatter_chunks(p, b, chunk, nvec, ltid, lsize);
   }
-  if (is_out) {
-    char* prev = lam_region(p, p.rank, pb);
-    rearm(prev, p.st->dirty_lo[pb], otid, osize);
-    rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], otid, osize);
-  }
+  if (is_out) rearm_previous(p, pb, otid, osize);
   if (TWOSHOT) {
     if (is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
     if (is_out)
@@ -714,17 +754,161 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
            TWOSHOT ? (unsigned long long)nvec * 16 : 0ull);
 }
 
+// ---- NVLS variant: the reduction happens inside the NVSwitch ----------------------------------
+//
+// Bandwidth regime.  Per rank and direction the push two-shot moves 2(N-1)/N * S over the link;
+// here every byte crosses once: the switch PULLS each rank's copy (multimem.ld_reduce: one request,
+// N reads, one reduced response) and REPLICATES the sums (multimem.st: one store, N writes).
+//
+//   LINK CTAs  for each pipeline group g (a sub-slice of every rank's chunk):
+//                copy-in   in -> xin (local HBM; the switch can only read the symmetric buffer)
+//                signal    last CTA: flag[g][rank] = epoch+1 on every rank (one multicast store)
+//              and one group behind:
+//                wait      flag[g-1][r] == epoch+1 for all r   (N threads poll N local flags)
+//                reduce    x = ld_reduce(mc xin) for my chunk's vectors; sums go to every
+//                          rank's sum region with ONE multimem.st each; data is its own flag
+//   ROW CTAs   re-arm the previous call's regions, poll the sum region row by row and run the
+//              residual + RMSNorm epilogue (or copy the sums out for the plain all-reduce)
+//
+// xin needs no double buffering: rank r can only start call k+1 after it has seen every sum of
+// call k, i.e. after every rank has finished reading xin for call k.  The sum regions rotate with
+// the epoch exactly like the arena regions (same proof).  The order in which the switch adds the
+// N values is not specified, so this variant is tolerance-parity with the oracle (north_star's
+// 1e-2; in practice the fp32 sums differ in the last bits before the one rounding), never
+// bit-parity; all ranks still get identical bits because each sum is computed once and broadcast.
+template <typename T, int VPT, bool FUSED>
+__device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
+  pdl_launch_dependents();
+  uint4 gam[VPT];
+  if (FUSED) load_gamma<T, VPT>(gam, p);
+  pdl_wait();
+
+  const CallState cs = begin_call(p);
+  const uint32_t epoch = cs.epoch;
+  const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;
+  const uint32_t tag = epoch + 1u;  // never 0: a zeroed flag can never satisfy a wait
+  const uint32_t nvec = (uint32_t)p.nvec;  // <= 2^28 vectors (4 GiB) by construction
+  const uint32_t world = (uint32_t)p.world;
+  const uint32_t chunk = (nvec + world - 1) / world;
+  const uint32_t G = (uint32_t)p.nv_groups;
+  const uint32_t sub = (chunk + G - 1) / G;
+  const int link_blocks = p.link_blocks;
+  const bool is_link = (int)blockIdx.x < link_blocks;
+  char* xin = p.nv_uc + kNvCtrlBytes;
+  const char* mc_xin = p.nv_mc + kNvCtrlBytes;
+  char* sum_uc = nv_sum_region(p.nv_uc, p, b);
+  char* sum_mc = nv_sum_region(p.nv_mc, p, b);
+  SpinGuard sg;
+
+  if (is_link) {
+    const uint32_t ltid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lsize = (uint32_t)link_blocks * blockDim.x;
+    constexpr int U = 4;
+    for (uint32_t g = 0; g <= G; ++g) {
+      if (g < G) {
+        const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk), n = v1 - v0;
+        const uint32_t total = n * world;
+        for (uint32_t base = ltid; base < total; base += lsize * U) {
+          uint4 v[U];
+          uint32_t idx[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const uint32_t i = base + (uint32_t)u * lsize;
+            idx[u] = nvec;
+            if (i < total) {
+              const uint32_t o = i / n;
+              idx[u] = o * chunk + v0 + (i - o * n);
+            }
+            if (idx[u] < nvec) v[u] = ld_stream_v4((const char*)p.in + (size_t)idx[u] * 16);
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (idx[u] < nvec) st_v4(xin + (size_t)idx[u] * 16, v[u]);
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          const uint32_t prev = atomicAdd(&p.st->nv_arrive[g], 1u);
+          if (prev == (uint32_t)link_blocks - 1u) {
+            p.st->nv_arrive[g] = 0;
+            __threadfence_system();
+            mc_st_release_u32(nv_flag(p.nv_mc, (int)g, p.rank), tag);
+          }
+        }
+      }
+      if (g >= 1) {
+        const uint32_t gg = g - 1;
+        if (threadIdx.x < world) {
+          const uint32_t* f = reinterpret_cast<const uint32_t*>(nv_flag(p.nv_uc, (int)gg, (int)threadIdx.x));
+          while (ld_acquire_sys(f) != tag)
+            if (sg.expired(p)) break;
+        }
+        __syncthreads();
+        const uint32_t v0 = min(gg * sub, chunk), v1 = min(v0 + sub, chunk);
+        const uint32_t my0 = (uint32_t)p.rank * chunk;
+        for (uint32_t base = v0 + ltid; base < v1; base += lsize * U) {
+          uint4 x[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const uint32_t v = base + (uint32_t)u * lsize;
+            if (v < v1 && my0 + v < nvec) x[u] = VecOps<T>::mc_ld_reduce(mc_xin + (size_t)(my0 + v) * 16);
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const uint32_t v = base + (uint32_t)u * lsize;
+            if (v < v1 && my0 + v < nvec) {
+              scrub(x[u]);
+              mc_st_v4(sum_mc + (size_t)(my0 + v) * 16, x[u]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    const int row0 = (int)blockIdx.x - link_blocks;
+    const int row_stride = (int)gridDim.x - link_blocks;
+    const size_t rtid = (size_t)row0 * blockDim.x + threadIdx.x;
+    const size_t rsize = (size_t)row_stride * blockDim.x;
+    rearm_previous(p, pb, rtid, rsize);
+    if (FUSED) {
+      int parity = 0;
+      for (int row = row0; row < p.tokens; row += row_stride) {
+        const size_t row_vec0 = (size_t)row * p.hv;
+        uint4 s[VPT], res[VPT];
+        load_residual<VPT>(res, row_vec0, p);
+#pragma unroll
+        for (int j = 0; j < VPT; ++j) {
+          const int c = threadIdx.x + j * blockDim.x;
+          if (c < p.hv) s[j] = wait_one(sum_uc + (row_vec0 + c) * 16, p, sg);
+        }
+        row_epilogue<T, VPT>(s, res, gam, row_vec0, p, smem, parity);
+      }
+    } else {
+      for (size_t idx = rtid; idx < nvec; idx += rsize)
+        st_v4((char*)p.out + idx * 16, wait_one(sum_uc + idx * 16, p, sg));
+    }
+  }
+  end_call(p, cs, 0ull, 0ull, (unsigned long long)nvec * 16);
+}
+
+template <typename T, int VPT, bool FUSED>
+__global__ void __launch_bounds__(512, B200C_TWOSHOT_CTAS_PER_SM)
+    nvls_kernel(const __grid_constant__ RankParams p) {
+  __shared__ float smem[64];  // 2 x 32 reduction banks
+  nvls_body<T, VPT, FUSED>(p, smem);
+}
+
 // ---- kernels: a real launch carries one rank, an emulated launch carries all of them ----------
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float smem[64];  // 2 x 32 reduction banks
   ar_norm_body<T, VPT, TWOSHOT>(p, smem);
 }
 
 template <typename T, int VPT, bool TWOSHOT>
 __global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) ar_norm_kernel_emu(const __grid_constant__ EmuParams ep) {
-  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float smem[64];  // 2 x 32 reduction banks
   ar_norm_body<T, VPT, TWOSHOT>(ep.r[blockIdx.y], smem);
 }
 
@@ -742,7 +926,7 @@ __global__ void __launch_bounds__(512, TWOSHOT ? B200C_TWOSHOT_CTAS_PER_SM : 1) 
 // residual add + RMSNorm on rows of `in` (res_in == nullptr: plain rms_norm).
 template <typename T, int VPT>
 __global__ void __launch_bounds__(512) norm_kernel(const __grid_constant__ RankParams p) {
-  __shared__ float smem[72];  // 2 x 32 reduction banks + the epoch broadcast slot
+  __shared__ float smem[64];  // 2 x 32 reduction banks
   pdl_launch_dependents();
   uint4 gam[VPT];
   load_gamma<T, VPT>(gam, p);
@@ -845,6 +1029,7 @@ struct CopyParams {
   unsigned long long row_vecs;  // 16-byte vectors per slab row
   unsigned long long nvec;      // p2p: message vectors
   unsigned long long timeout_ns;
+  int trap;  // policy when a wait times out (see SpinGuard)
   int role;  // emu sendrecv: 0 = sender, 1 = receiver
 };
 
@@ -859,7 +1044,7 @@ __device__ __forceinline__ uint32_t* ctrl_flag(char* arena, size_t off, int i) {
 __device__ __forceinline__ void wait_flag_ge(const uint32_t* f, uint32_t want, const CopyParams& p,
                                              SpinGuard& sg) {
   while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
-    if (sg.expired(p.timeout_ns, &p.st->error)) break;
+    if (sg.expired(p)) break;
   }
 }
 
