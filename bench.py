@@ -360,8 +360,9 @@ def run_ours(args) -> dict:
         per_call_us = round(ms_ar * 1e3 / calls, 3)
         gather_us = round(ms_ag * 1e3, 3)
     if extras:
-        reps = 8
         for tokens in (B, big_tokens):
+            # enough calls per graph that the graph's own launch cost (~10 us) disappears
+            reps = 8 if tokens * H * 2 > (4 << 20) else 64
             xb = torch.randn(tokens, H, generator=gen).bfloat16().to(dev)
             rb = torch.randn(tokens, H, generator=g7).bfloat16().to(dev)
             hb = torch.empty_like(xb)
@@ -493,6 +494,12 @@ def _ref_worker(rank, world, port, shp, B, calls, steps, warmup, use_vllm, q):
     try:
         if not use_vllm:
             raise RuntimeError("vllm path disabled")
+        # This arm times vLLM's CPU (gloo) communicator path.  On a GPU box vLLM's platform
+        # detection (NVML sees GPUs even with CUDA_VISIBLE_DEVICES="") would pick CudaPlatform
+        # and then fail to build its NCCL communicator; switch the CUDA detector off so that the
+        # platform resolves exactly as on a CPU-only host (where the golden fixtures were made).
+        import vllm.platforms as vllm_platforms
+        vllm_platforms.builtin_platform_plugins["cuda"] = lambda: None
         from vllm.config import DeviceConfig, VllmConfig, set_current_vllm_config
         from vllm.distributed import parallel_state as ps
         from vllm.distributed.communication_op import (tensor_model_parallel_all_gather,
@@ -508,7 +515,8 @@ def _ref_worker(rank, world, port, shp, B, calls, steps, warmup, use_vllm, q):
         ag = tensor_model_parallel_all_gather
         norm = irops.fused_add_rms_norm
     except Exception as e:  # vLLM's CPU path unusable on this box: time the port instead
-        kind = f"port ({type(e).__name__})"
+        kind = f"port ({type(e).__name__}: {str(e)[:160]})"
+        log(f"[reference arm rank {rank}] vLLM CPU path unusable, timing the port instead: {e!r}")
         import torch.distributed as dist
         if not dist.is_initialized():
             dist.init_process_group("gloo", rank=rank, world_size=world,

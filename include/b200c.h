@@ -62,8 +62,12 @@ extern "C" {
                                           executes `trap`, so the next CUDA call of the process fails    */
 
 #define B200C_TUNE_NVLS_MIN_BYTES 11   /* AUTO picks NVLS at or above this size; < 0 (default) = never  */
-#define B200C_TUNE_NVLS_LINK_BLOCKS 12 /* NVLS CTAs doing copy-in + in-switch reduce; 0 = half the grid */
+#define B200C_TUNE_NVLS_LINK_BLOCKS 12 /* NVLS CTAs doing the in-switch reduce + broadcast; 0 = grid/6    */
 #define B200C_TUNE_NVLS_GROUPS 13      /* NVLS copy-in pipeline groups (1..8); 0 = by size               */
+#define B200C_TUNE_NVLS_COPY_BLOCKS 14 /* NVLS CTAs copying the input into the symmetric buffer; 0 = grid/6 */
+#define B200C_TUNE_NVLS_TEAMS 15       /* NVLS reduce CTAs work in this many teams (1..8), each on its own group; 0 = 4 */
+#define B200C_TUNE_NVLS_DEBUG 16       /* measurement only, results are garbage: 1 no copy-in, 2 no ld_reduce, \
+                                          4 no multimem.st, 8 no consumer */
 
 typedef struct b200c_ctx b200c_ctx;
 

@@ -34,7 +34,7 @@ def test_no_cuda_needed_for_metadata_calls():
     # + 8*2 mailboxes
     assert out.value == 64 * 1024 + 6 * ((1 << 20) + 256) + 2 * (1 << 20) + 16 * (1 << 20)
     assert lib.b200c_nvls_bytes(1 << 20, ctypes.byref(out)) == 0
-    assert out.value == 16 * 1024 + 4 * ((1 << 20) + 256)  # flags + xin + 3 rotating sum regions
+    assert out.value == 32 * 1024 + (1 << 20) + 256  # two flag tables + xin (sums are written in place)
     assert lib.b200c_arena_bytes(9, 16, 16, 16, ctypes.byref(out)) == C.EINVAL
     assert b"world" in lib.b200c_last_error()
 
@@ -48,5 +48,6 @@ def test_header_constants_match_binding():
               "ETIMEOUT", "ENOMEM", "TUNE_ONESHOT_MAX_BYTES", "TUNE_ONESHOT_BLOCKS",
               "TUNE_TWOSHOT_BLOCKS", "TUNE_SPIN_TIMEOUT_MS", "TUNE_COPY_BLOCKS", "TUNE_LINK_BLOCKS",
               "TUNE_PDL", "TUNE_ONESHOT_SPLIT", "TUNE_DEBUG_EPOCH", "NVLS", "TUNE_TRAP_ON_TIMEOUT",
-              "TUNE_NVLS_MIN_BYTES", "TUNE_NVLS_LINK_BLOCKS", "TUNE_NVLS_GROUPS"):
+              "TUNE_NVLS_MIN_BYTES", "TUNE_NVLS_LINK_BLOCKS", "TUNE_NVLS_GROUPS",
+              "TUNE_NVLS_COPY_BLOCKS", "TUNE_NVLS_TEAMS", "TUNE_NVLS_DEBUG"):
         assert int(consts[k]) == getattr(C, k), k

@@ -86,6 +86,9 @@ def main():
     ap.add_argument("--link", type=int, nargs="+", default=[24, 48, 74, 110])
     ap.add_argument("--no-flashinfer", action="store_true")
     ap.add_argument("--no-vllm-ca", action="store_true")
+    ap.add_argument("--no-symm-mem", action="store_true")
+    ap.add_argument("--nvls-grid", type=str, nargs="+", default=["0:0", "24:24", "48:48", "32:64", "64:32", "74:74"],
+                    help="NVLS copy:reduce CTA counts to try (0:0 = the library's default)")
     ap.add_argument("--pdl", type=int, nargs="+", default=[1, 0])
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
@@ -99,8 +102,26 @@ def main():
     cpu = dist.new_group(backend="gloo")
     max_bytes = args.max_tokens * max(args.hidden) * 2
     comm = bc.B200Comm.from_process_group(cpu, dev, max_bytes=max_bytes, ag_bytes=1 << 20,
-                                          p2p_bytes=1 << 20)
+                                          p2p_bytes=1 << 20, device_group=dist.group.WORLD)
     comm.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, 5000)
+    defaults = {k: comm.get_tuning(k) for k in (C.TUNE_ONESHOT_BLOCKS, C.TUNE_TWOSHOT_BLOCKS,
+                                                C.TUNE_LINK_BLOCKS, C.TUNE_ONESHOT_SPLIT, C.TUNE_PDL)}
+    if rank == 0:
+        print(f"NVLS multicast: {'attached' if comm.nvls else 'not available'}", file=sys.stderr)
+
+    # K7: stock vLLM's choice above 1-2 MiB on cc 10.0 -- torch symmetric memory, in-switch
+    # reduction, with its copy-in / copy-out (symm_mem.py:119-154)
+    k7 = None
+    if not args.no_symm_mem:
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            k7_buf = symm_mem.empty(max_bytes // 2, dtype=torch.bfloat16, device=dev)
+            k7_hdl = symm_mem.rendezvous(k7_buf, dist.group.WORLD.group_name)
+            if k7_hdl.multicast_ptr:
+                k7 = (k7_buf, dist.group.WORLD.group_name)
+        except Exception as e:  # noqa: BLE001
+            if rank == 0:
+                print(f"symm_mem comparator unavailable: {type(e).__name__}: {e}", file=sys.stderr)
 
     fi = None
     if not args.no_flashinfer:
@@ -138,7 +159,7 @@ def main():
     rows = []
     tokens = [1 << i for i in range(0, 14) if (1 << i) <= args.max_tokens]
     if args.quick:
-        tokens = [t for t in tokens if t in (1, 16, 64, 256, 1024, 4096)]
+        tokens = [t for t in tokens if t in (1, 16, 64, 256, 1024, 4096, 8192)]
     NBUF = 4
     for H in args.hidden:
         gamma = torch.randn(H, device=dev).bfloat16()
@@ -176,6 +197,24 @@ def main():
                     best = us if best is None else min(best, us)
             comm.set_tuning(C.TUNE_LINK_BLOCKS, 0)
             row["twoshot_us"] = round(best, 2)
+            # what AUTO runs with nothing tuned: the number a user of the library gets
+            for k, v in defaults.items():
+                comm.set_tuning(k, v)
+            row["auto_us"] = round(time_graph(ours(C.AUTO), iters, 3, dev, n), 2)
+            if comm.nvls:
+                best_nv = None
+                for spec in args.nvls_grid:
+                    cpy, red = (int(v) for v in spec.split(":"))
+                    comm.set_tuning(C.TUNE_NVLS_COPY_BLOCKS, cpy)
+                    comm.set_tuning(C.TUNE_NVLS_LINK_BLOCKS, red)
+                    us = time_graph(ours(C.NVLS), iters, 3, dev, n)
+                    row[f"nvls_c{cpy}_r{red}_us"] = round(us, 2)
+                    best_nv = us if best_nv is None else min(best_nv, us)
+                comm.set_tuning(C.TUNE_NVLS_COPY_BLOCKS, 0)
+                comm.set_tuning(C.TUNE_NVLS_LINK_BLOCKS, 0)
+                row["nvls_us"] = round(best_nv, 2)
+                row["ar_nvls_us"] = round(time_graph(
+                    lambda i: comm.all_reduce(xs[i % NBUF], C.NVLS, out), iters, 3, dev, n), 2)
             # plain all-reduce (no epilogue), both variants at default CTA counts
             comm.set_tuning(C.TUNE_ONESHOT_BLOCKS, 148)
             comm.set_tuning(C.TUNE_TWOSHOT_BLOCKS, 148)
@@ -197,6 +236,25 @@ def main():
                 bc.fused_add_rms_norm_(tmp[i % NBUF], res, gamma, 1e-5)
             row["nccl_ar_us"] = round(time_graph(nccl_only, iters, 3, dev, n), 2)
             row["nccl_pair_us"] = round(time_graph(nccl_pair, iters, 3, dev, n), 2)
+
+            if k7 is not None:
+                try:
+                    kbuf, gname = k7
+                    view = kbuf[: T * H]
+                    o7 = torch.empty(T, H, dtype=torch.bfloat16, device=dev)
+
+                    def k7_only(i):
+                        view.copy_(xs[i % NBUF].view(-1))
+                        torch.ops.symm_mem.multimem_all_reduce_(view, "sum", gname)
+                        o7.copy_(view.view(T, H))
+
+                    def k7_pair(i):
+                        k7_only(i)
+                        bc.fused_add_rms_norm_(o7, res, gamma, 1e-5)
+                    row["symm_mem_ar_us"] = round(time_graph(k7_only, iters, 3, dev, n), 2)
+                    row["symm_mem_pair_us"] = round(time_graph(k7_pair, iters, 3, dev, n), 2)
+                except Exception as e:  # noqa: BLE001
+                    row["symm_mem_error"] = f"{type(e).__name__}: {e}"[:200]
 
             if ca is not None and S <= (8 << 20):
                 try:
@@ -227,7 +285,7 @@ def main():
                 except Exception as e:  # noqa: BLE001
                     row["flashinfer_error"] = f"{type(e).__name__}: {e}"[:200]
             bus = 2 * (n - 1) / n * S
-            best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us"))
+            best = min(v for k, v in row.items() if k in ("oneshot_us", "twoshot_us", "nvls_us"))
             row["best_us"] = best
             row["bus_gbs"] = round(bus / best / 1e3, 1)
             rows.append(row)

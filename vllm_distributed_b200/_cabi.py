@@ -22,6 +22,7 @@ TUNE_ONESHOT_MAX_BYTES, TUNE_ONESHOT_BLOCKS, TUNE_TWOSHOT_BLOCKS = 1, 2, 3
 TUNE_SPIN_TIMEOUT_MS, TUNE_COPY_BLOCKS = 4, 5
 TUNE_LINK_BLOCKS, TUNE_PDL, TUNE_ONESHOT_SPLIT, TUNE_DEBUG_EPOCH = 6, 7, 8, 9
 TUNE_TRAP_ON_TIMEOUT, TUNE_NVLS_MIN_BYTES, TUNE_NVLS_LINK_BLOCKS, TUNE_NVLS_GROUPS = 10, 11, 12, 13
+TUNE_NVLS_COPY_BLOCKS, TUNE_NVLS_TEAMS, TUNE_NVLS_DEBUG = 14, 15, 16
 NOALLOC_MAX_BYTES = 64 * 1024
 
 Handle = c_ubyte * IPC_HANDLE_BYTES

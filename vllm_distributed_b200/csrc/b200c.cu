@@ -82,8 +82,11 @@ struct b200c_ctx {
   char* nv_mc = nullptr;
   size_t nv_half = 0;
   long long nvls_min_bytes = -1;  // AUTO picks NVLS at or above this size; < 0 = never
-  int nvls_link_blocks = 0;       // 0 = half of the grid
+  int nvls_link_blocks = 0;       // reduce CTAs; 0 = a sixth of the grid
+  int nvls_copy_blocks = 0;       // copy-in CTAs; 0 = a sixth of the grid
   int nvls_groups = 0;            // copy-in pipeline groups; 0 = by size
+  int nvls_teams = 0;             // reduce teams; 0 = 4
+  int nvls_debug = 0;             // measurement only: phase-skipping bits
 };
 
 namespace {
@@ -350,10 +353,10 @@ int launch_ar_norm_cluster(b200c_ctx* const* ctxs, int nemu, const RankParams* r
 // ---- NVLS variant (real ranks only: a multicast group has one member per device) -------------
 int nvls_groups_for(const b200c_ctx* c, size_t bytes) {
   if (c->nvls_groups > 0) return std::min(c->nvls_groups, kNvMaxGroups);
-  // one group below 4 MiB (the flag round trip costs more than the copy-in it would hide);
-  // above, about 1 MiB of the message per group
-  int g = (int)std::min<size_t>(kNvMaxGroups, bytes >> 20);
-  return bytes < (size_t)(4u << 20) ? 1 : std::max(1, g);
+  // Every group costs each copy CTA a system fence, an atomic and (the last one) a multicast
+  // flag store -- about 12 us per group measured on 8 x B200 (tools/nvls_probe.py) -- so groups
+  // only pay when a group's link time is well above that: one per 16 MiB, at most 4.
+  return (int)std::max<size_t>(1, std::min<size_t>(4, bytes >> 24));
 }
 
 template <typename K>
@@ -363,9 +366,18 @@ int launch_nvls_k(K kernel, b200c_ctx* c, RankParams p, size_t bytes, cudaStream
   int rc = coresident_blocks(kernel, threads, c->sm_count, &cap);
   if (rc) return rc;
   const int g = std::max(2, std::min(twoshot_grid(c, bytes), cap));
-  const int l = c->nvls_link_blocks > 0 ? c->nvls_link_blocks : g / 2;
-  p.link_blocks = std::max(1, std::min(l, g - 1));
+  // roles (tools/nvls_bench.cu): about an eighth of the grid saturates the link on the reduce
+  // side (more CTAs only add contention); every other CTA copies in and then consumes
   p.nv_groups = nvls_groups_for(c, bytes);
+  int red = c->nvls_link_blocks > 0 ? c->nvls_link_blocks : std::max(1, g / 8);
+  red = std::max(1, std::min(red, g - 1));
+  int teams = c->nvls_teams > 0 ? c->nvls_teams : 4;
+  teams = std::max(1, std::min(teams, std::min(p.nv_groups, red)));
+  red = red / teams * teams;  // equal teams
+  p.link_blocks = red;
+  p.nv_copy_blocks = g - red;
+  p.nv_teams = teams;
+  p.nv_debug = c->nvls_debug;
   return launch(kernel, dim3(g, 1, 1), threads, p, s, false, c->pdl != 0);
 }
 
@@ -730,7 +742,7 @@ int b200c_destroy(b200c_ctx* c) {
 
 int b200c_nvls_bytes(size_t max_bytes, size_t* out_bytes) {
   if (!out_bytes) return fail(B200C_EINVAL, "out_bytes is NULL");
-  *out_bytes = kNvCtrlBytes + 4 * region_half(max_bytes);
+  *out_bytes = kNvCtrlBytes + region_half(max_bytes);
   return B200C_OK;
 }
 
@@ -740,15 +752,12 @@ int b200c_attach_nvls(b200c_ctx* c, void* uc_ptr, void* mc_ptr, size_t bytes) {
   if (!uc_ptr || !mc_ptr || !aligned16(uc_ptr) || !aligned16(mc_ptr))
     return fail(B200C_EINVAL, "NULL or misaligned NVLS buffer");
   const size_t half = region_half(c->max_bytes);
-  if (bytes < kNvCtrlBytes + 4 * half)
+  if (bytes < kNvCtrlBytes + half)
     return fail(B200C_ETOOBIG, "NVLS buffer of %zu bytes is smaller than the %zu this ctx needs", bytes,
-                kNvCtrlBytes + 4 * half);
+                kNvCtrlBytes + half);
   char* uc = static_cast<char*>(uc_ptr);
-  // own copy: flags to zero, sum regions to "not arrived" (through the unicast mapping only)
+  // own copy of the flags to zero (through the unicast mapping only); the data area needs no arming
   CUDA_TRY(cudaMemset(uc, 0, kNvCtrlBytes));
-  fill_not_arrived_kernel<<<c->sm_count * 4, 256>>>(reinterpret_cast<uint4*>(uc + kNvCtrlBytes + half),
-                                                   3 * half / 16);
-  CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaDeviceSynchronize());
   c->nv_uc = uc;
   c->nv_mc = static_cast<char*>(mc_ptr);
@@ -771,6 +780,9 @@ int b200c_set_tuning(b200c_ctx* c, int key, long long v) {
     case B200C_TUNE_NVLS_MIN_BYTES: c->nvls_min_bytes = v; break;
     case B200C_TUNE_NVLS_LINK_BLOCKS: c->nvls_link_blocks = (int)std::max<long long>(0, v); break;
     case B200C_TUNE_NVLS_GROUPS: c->nvls_groups = (int)std::max<long long>(0, std::min<long long>(kNvMaxGroups, v)); break;
+    case B200C_TUNE_NVLS_COPY_BLOCKS: c->nvls_copy_blocks = (int)std::max<long long>(0, v); break;
+    case B200C_TUNE_NVLS_TEAMS: c->nvls_teams = (int)std::max<long long>(0, std::min<long long>(kNvMaxGroups, v)); break;
+    case B200C_TUNE_NVLS_DEBUG: c->nvls_debug = (int)v; break;
     case B200C_TUNE_DEBUG_EPOCH: {
       // test hook (host-synchronous): jump the all-reduce call counter, e.g. to just below 2^32
       if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
@@ -799,6 +811,9 @@ int b200c_get_tuning(b200c_ctx* c, int key, long long* v) {
     case B200C_TUNE_NVLS_MIN_BYTES: *v = c->nvls_min_bytes; break;
     case B200C_TUNE_NVLS_LINK_BLOCKS: *v = c->nvls_link_blocks; break;
     case B200C_TUNE_NVLS_GROUPS: *v = c->nvls_groups; break;
+    case B200C_TUNE_NVLS_COPY_BLOCKS: *v = c->nvls_copy_blocks; break;
+    case B200C_TUNE_NVLS_TEAMS: *v = c->nvls_teams; break;
+    case B200C_TUNE_NVLS_DEBUG: *v = c->nvls_debug; break;
     case B200C_TUNE_DEBUG_EPOCH: {
       if (!c->st) return fail(B200C_EINVAL, "no device state (world == 1)");
       unsigned long long w = 0;

@@ -41,10 +41,9 @@ struct LocalState {
   unsigned long long dirty_hi[3];
   uint32_t send_seq[kMaxRanks];
   uint32_t recv_seq[kMaxRanks];
-  // NVLS variant: CTA arrival counters of the copy-in groups, and the bytes the switch wrote
-  // into each rotating sum region of the NVLS buffer (0 after a call of another variant)
+  // NVLS variant: CTA arrival counters of the copy-in groups and of the reduce slices
   uint32_t nv_arrive[8];
-  unsigned long long nv_dirty[3];
+  uint32_t nv_arrive_red[8];
 };
 
 struct RankParams {
@@ -72,6 +71,9 @@ struct RankParams {
   char* nv_mc;
   size_t nv_half;
   int nv_groups;
+  int nv_copy_blocks;  // unused (every non-reduce CTA copies in, then consumes)
+  int nv_teams;        // reduce CTAs work in this many teams, each on its own group
+  int nv_debug;        // measurement only (B200C_TUNE_NVLS_DEBUG): skip phases, results are garbage
 };
 
 struct EmuParams {
@@ -155,29 +157,28 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
 
 
 // ---- NVLS buffer layout (bytes from its base; identical on every rank) ---------------------------
-// [0, 16K)       flags [8 groups][8 src], one per 128-byte line: flag[g][r] = epoch+1 of the last
-//                call whose copy-in group g rank r has completed (written through the multicast
-//                mapping, so one store updates every rank's copy)
-// 1 x nv_half    xin: this rank's input, copied in so that the switch can read it
-// 3 x nv_half    rotating sum regions, region = epoch % 3, armed with "not arrived"
-constexpr size_t kNvCtrlBytes = 16 * 1024;
+// [0, 16K)       flagA [8 groups][8 src], one per 128-byte line: flagA[g][r] = epoch+1 of the last
+//                call in which rank r has finished copying group g of its input into xin
+// [16K, 32K)     flagB [8 groups][8 owner]: flagB[g][o] = epoch+1 of the last call in which owner o
+//                has broadcast the sums of slice g of its chunk
+//                (both are written through the multicast mapping: one store updates every rank)
+// 1 x nv_half    xin: this rank's input, copied in so that the switch can read it; the sums are
+//                written back IN PLACE (by multicast) and consumed from here
+constexpr size_t kNvCtrlBytes = 32 * 1024;
+constexpr size_t kNvFlagBOff = 16 * 1024;
 constexpr int kNvMaxGroups = 8;
 
-__device__ __forceinline__ char* nv_sum_region(char* base, const RankParams& p, uint32_t b) {
-  return base + kNvCtrlBytes + (size_t)(1u + b) * p.nv_half;
-}
 __device__ __forceinline__ char* nv_flag(char* base, int group, int src) {
   return base + ((size_t)group * kMaxRanks + src) * kFlagStride;
 }
 
-// Re-arm everything the previous call dirtied: its arena region (push variants) and its sum
-// region in the NVLS buffer (NVLS variant); at most one of the extents is non-zero.
+// Re-arm the arena region the previous call dirtied (nothing after an NVLS call, which keeps
+// its data in the symmetric buffer and signals with flags).
 __device__ __forceinline__ void rearm_previous(const RankParams& p, uint32_t pb, size_t tid,
                                                size_t nthreads) {
   char* prev = lam_region(p, p.rank, pb);
   rearm(prev, p.st->dirty_lo[pb], tid, nthreads);
   rearm(prev + p.g.hi_off, p.st->dirty_hi[pb], tid, nthreads);
-  if (p.nv_uc != nullptr) rearm(nv_sum_region(p.nv_uc, p, pb), p.st->nv_dirty[pb], tid, nthreads);
 }
 
 // Call bookkeeping without an end-of-kernel rendezvous and without a fence: the epoch (high
@@ -208,13 +209,11 @@ __device__ __forceinline__ CallState begin_call(const RankParams& p) {
 }
 
 __device__ __forceinline__ void end_call(const RankParams& p, const CallState& cs,
-                                         unsigned long long dlo, unsigned long long dhi,
-                                         unsigned long long dnv = 0ull) {
+                                         unsigned long long dlo, unsigned long long dhi) {
   if (threadIdx.x == 0 && cs.ticket == gridDim.x - 1) {
     const uint32_t b = cs.epoch % 3u;
     p.st->dirty_lo[b] = dlo;
     p.st->dirty_hi[b] = dhi;
-    p.st->nv_dirty[b] = dnv;
     // 0xffffffff is a multiple of 3: wrapping from 0xfffffffe straight to 0 keeps the region
     // sequence ... 1, 2, 0 ... intact after 2^32 calls (about a week of 70B decode)
     const uint32_t next = (cs.epoch + 1u == 0xffffffffu) ? 0u : cs.epoch + 1u;
@@ -418,6 +417,34 @@ __device__ __forceinline__ void reduce_gather(const RankParams& p, uint32_t b, c
     reduce_gather_range<T, 1, 7>(p, b, my_lo, chunk, lo, hi, tid, nthreads, sg);
 }
 
+
+// ---- consumers walk the result in the order it ARRIVES ------------------------------------------
+// Every rank reduces its own chunk front to back at the same time, so at any moment the first
+// part of EVERY chunk has arrived.  A consumer that walks rows (or vectors) 0, 1, 2, ... waits
+// on the tail of chunk 0 while the heads of chunks 1..N-1 sit ready, and is left with (N-1)/N of
+// its work when the last sum lands.  ArrivalOrder interleaves the chunks slice by slice
+// (G slices per chunk): position q -> unit = owner * per_chunk + slice * per_slice + j.
+// Only the ORDER depends on it; which units exist does not (out-of-range positions return -1).
+struct ArrivalOrder {
+  uint32_t per_chunk, per_slice, per_round, total, units;
+  __device__ __forceinline__ ArrivalOrder(uint32_t units_, uint32_t world, uint32_t slices) {
+    units = units_;
+    per_chunk = (units_ + world - 1) / world;
+    per_slice = (per_chunk + slices - 1) / slices;
+    per_round = per_slice * world;
+    total = per_round * slices;
+  }
+  __device__ __forceinline__ long long at(uint32_t q) const {
+    const uint32_t g = q / per_round, rem = q - g * per_round;
+    const uint32_t o = rem / per_slice, j = rem - o * per_slice;
+    const uint32_t within = g * per_slice + j;
+    if (within >= per_chunk) return -1;
+    const uint32_t u = o * per_chunk + within;
+    return u < units ? (long long)u : -1;
+  }
+};
+constexpr uint32_t kArrivalSlices = 8;
+
 // ---- row epilogue: residual add + RMSNorm ------------------------------------------------------
 // s[j] holds the T-rounded all-reduce sum for vector (tid + j*blockDim) of the row, res[j] the
 // residual vector (prefetched before the wait), gam[j] the weight vector (loaded once per CTA).
@@ -548,9 +575,14 @@ __device__ __forceinline__ void ar_norm_body(const RankParams& p, float* smem) {
   // ---- two-shot: reduce my chunk, push the sums to every rank's hi half
   if (TWOSHOT && is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
 
-  // ---- rows: wait for the sums, epilogue
+  // ---- rows: wait for the sums, epilogue (two-shot: in the order the sums arrive)
   if (is_row) {
-    for (int row = row0; row < p.tokens; row += row_stride) {
+    const ArrivalOrder order((uint32_t)p.tokens, TWOSHOT ? (uint32_t)p.world : 1u,
+                             TWOSHOT ? kArrivalSlices : 1u);
+    for (uint32_t q = (uint32_t)row0; q < order.total; q += (uint32_t)row_stride) {
+      const long long rq = order.at(q);
+      if (rq < 0) continue;
+      const int row = (int)rq;
       const size_t row_vec0 = (size_t)row * p.hv;
       uint4 s[VPT], res[VPT];
       load_residual<VPT>(res, row_vec0, p);  // in flight while we wait on the peers
@@ -740,9 +772,13 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
   if (is_out) rearm_previous(p, pb, otid, osize);
   if (TWOSHOT) {
     if (is_link) reduce_gather<T>(p, b, my_lo, chunk, nvec, ltid, lsize, sg);
-    if (is_out)
-      for (size_t idx = otid; idx < nvec; idx += osize)
-        st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
+    if (is_out) {
+      const ArrivalOrder order((uint32_t)nvec, (uint32_t)p.world, kArrivalSlices);
+      for (size_t q = otid; q < order.total; q += osize) {
+        const long long idx = order.at((uint32_t)q);
+        if (idx >= 0) st_v4((char*)p.out + idx * 16, wait_one(my_hi + idx * 16, p, sg));
+      }
+    }
   } else {
     for (size_t idx = gtid; idx < nvec; idx += gsize) {
       const uint4 own = ld_v4((const char*)p.in + idx * 16);
@@ -756,26 +792,56 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
 
 // ---- NVLS variant: the reduction happens inside the NVSwitch ----------------------------------
 //
-// Bandwidth regime.  Per rank and direction the push two-shot moves 2(N-1)/N * S over the link;
-// here every byte crosses once: the switch PULLS each rank's copy (multimem.ld_reduce: one request,
-// N reads, one reduced response) and REPLICATES the sums (multimem.st: one store, N writes).
+// Bandwidth regime, large groups.  Per rank and direction the push two-shot moves 2(N-1)/N * S
+// over the link; here the switch PULLS each rank's copy (multimem.ld_reduce: one request, N reads,
+// one reduced response) and REPLICATES the sums (multimem.st: one store, N writes), which costs
+// (1 + 1/N) * S per direction -- the own copy also travels to the switch and back.  Measured
+// with tools/nvls_bench.cu: ld_reduce is bound by the outbound link, multimem.st by the inbound
+// one, so the two overlap; at N = 2 NVLS moves MORE than the push kernels (1.5 S vs S) and is
+// never chosen, at N = 8 it moves 1.125 S vs 1.75 S.
 //
-//   LINK CTAs  for each pipeline group g (a sub-slice of every rank's chunk):
-//                copy-in   in -> xin (local HBM; the switch can only read the symmetric buffer)
-//                signal    last CTA: flag[g][rank] = epoch+1 on every rank (one multicast store)
-//              and one group behind:
-//                wait      flag[g-1][r] == epoch+1 for all r   (N threads poll N local flags)
-//                reduce    x = ld_reduce(mc xin) for my chunk's vectors; sums go to every
-//                          rank's sum region with ONE multimem.st each; data is its own flag
-//   ROW CTAs   re-arm the previous call's regions, poll the sum region row by row and run the
-//              residual + RMSNorm epilogue (or copy the sums out for the plain all-reduce)
+// Everything here is sized for bandwidth, so arrival is signalled with FLAGS, not with the
+// data itself: no region has to be re-armed (S bytes of stores per call), nothing is scrubbed,
+// and consumers stream whole slices with several loads in flight instead of polling vector by
+// vector (one L2 round trip per 16 bytes per thread).
 //
-// xin needs no double buffering: rank r can only start call k+1 after it has seen every sum of
-// call k, i.e. after every rank has finished reading xin for call k.  The sum regions rotate with
-// the epoch exactly like the arena regions (same proof).  The order in which the switch adds the
-// N values is not specified, so this variant is tolerance-parity with the oracle (north_star's
-// 1e-2; in practice the fp32 sums differ in the last bits before the one rounding), never
-// bit-parity; all ranks still get identical bits because each sum is computed once and broadcast.
+// Two kinds of CTA; waits only ever point from later work to earlier work (copy -> reduce ->
+// consume), the copy never waits, and the grid is co-resident, so the kernel cannot deadlock:
+//   COPY/ROW CTAs  first stream the input into xin (the switch can only read the symmetric
+//                buffer), one pipeline group after the other; after each group the last CTA to
+//                finish stores flagA[g][rank] = epoch+1 on every rank with ONE multicast store.
+//                Then they turn into ROW CTAs (below).
+//   REDUCE CTAs  per group: N threads wait for the N local flagA, then x = ld_reduce(mc xin) for
+//                my chunk's vectors of that group, written back IN PLACE on every rank with ONE
+//                multimem.st per vector; the last CTA to finish the slice stores
+//                flagB[g][rank] = epoch+1 everywhere
+//   ROW CTAs     (the copy CTAs, once done) walk the rows in arrival order (ArrivalOrder), wait for the flagB of the slice a
+//                vector lies in (remembered, so once per slice), read the sums from xin and run
+//                the residual + RMSNorm epilogue (or copy them out for the plain all-reduce)
+//
+// Hazards.  xin is overwritten by the next call's copy-in: a rank starts call k+1 only after it
+// has seen every flagB of call k, i.e. after every owner's stores were performed everywhere
+// (release), which in turn follow that owner's ld_reduce of the same addresses.  Writing the sums
+// over xin is safe because only the owner ever reads its chunk through the switch.  Flags carry
+// epoch+1 and are compared modulo 2^32 (flag - tag >= 0), so no flag is ever reset.  The switch
+// rounds ties differently from round-to-nearest-even and its summation order is unspecified, so
+// this variant is tolerance-parity with the oracle (north_star's 1e-2), never bit-parity; all
+// ranks still get identical bits because each sum is computed once and broadcast.
+struct SliceGate {
+  uint32_t seen = 0xffffffffu;  // slice id this thread has already found complete
+  template <typename P>
+  __device__ __forceinline__ void wait(const P& p, uint32_t idx, uint32_t chunk, uint32_t sub,
+                                       uint32_t tag, SpinGuard& sg) {
+    const uint32_t o = idx / chunk, g = (idx - o * chunk) / sub;
+    const uint32_t id = g * kMaxRanks + o;
+    if (id == seen) return;
+    const uint32_t* f = reinterpret_cast<const uint32_t*>(nv_flag(p.nv_uc + kNvFlagBOff, (int)g, (int)o));
+    while ((int32_t)(ld_acquire_sys(f) - tag) < 0)
+      if (sg.expired(p)) break;
+    seen = id;
+  }
+};
+
 template <typename T, int VPT, bool FUSED>
 __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
   pdl_launch_dependents();
@@ -785,110 +851,156 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
 
   const CallState cs = begin_call(p);
   const uint32_t epoch = cs.epoch;
-  const uint32_t b = epoch % 3u, pb = (b + 2u) % 3u;
+  const uint32_t pb = (epoch % 3u + 2u) % 3u;
   const uint32_t tag = epoch + 1u;  // never 0: a zeroed flag can never satisfy a wait
   const uint32_t nvec = (uint32_t)p.nvec;  // <= 2^28 vectors (4 GiB) by construction
   const uint32_t world = (uint32_t)p.world;
   const uint32_t chunk = (nvec + world - 1) / world;
   const uint32_t G = (uint32_t)p.nv_groups;
   const uint32_t sub = (chunk + G - 1) / G;
-  const int link_blocks = p.link_blocks;
-  const bool is_link = (int)blockIdx.x < link_blocks;
+  const int red_blocks = p.link_blocks;            // CTAs [0, red_blocks) reduce
+  const int copy_blocks = (int)gridDim.x - red_blocks;  // everybody else copies in, then consumes
   char* xin = p.nv_uc + kNvCtrlBytes;
-  const char* mc_xin = p.nv_mc + kNvCtrlBytes;
-  char* sum_uc = nv_sum_region(p.nv_uc, p, b);
-  char* sum_mc = nv_sum_region(p.nv_mc, p, b);
+  char* mc_xin = p.nv_mc + kNvCtrlBytes;
   SpinGuard sg;
+  constexpr int U = 4;
 
-  if (is_link) {
-    const uint32_t ltid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t lsize = (uint32_t)link_blocks * blockDim.x;
-    constexpr int U = 4;
-    for (uint32_t g = 0; g <= G; ++g) {
-      if (g < G) {
-        const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk), n = v1 - v0;
-        const uint32_t total = n * world;
-        for (uint32_t base = ltid; base < total; base += lsize * U) {
-          uint4 v[U];
-          uint32_t idx[U];
+  if ((int)blockIdx.x >= red_blocks) {
+    // ---- COPY: sub-slice g of EVERY rank's chunk, group after group
+    const uint32_t ctid = (blockIdx.x - red_blocks) * blockDim.x + threadIdx.x;
+    const uint32_t csize = (uint32_t)copy_blocks * blockDim.x;
+    for (uint32_t g = 0; g < G; ++g) {
+      const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk), n = v1 - v0;
+      const uint32_t total = (p.nv_debug & 1) ? 0u : n * world;
+      for (uint32_t base = ctid; base < total; base += csize * U) {
+        uint4 v[U];
+        uint32_t idx[U];
 #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const uint32_t i = base + (uint32_t)u * lsize;
-            idx[u] = nvec;
-            if (i < total) {
-              const uint32_t o = i / n;
-              idx[u] = o * chunk + v0 + (i - o * n);
-            }
-            if (idx[u] < nvec) v[u] = ld_stream_v4((const char*)p.in + (size_t)idx[u] * 16);
+        for (int u = 0; u < U; ++u) {
+          const uint32_t i = base + (uint32_t)u * csize;
+          idx[u] = nvec;
+          if (i < total) {
+            const uint32_t o = i / n;
+            idx[u] = o * chunk + v0 + (i - o * n);
           }
-#pragma unroll
-          for (int u = 0; u < U; ++u)
-            if (idx[u] < nvec) st_v4(xin + (size_t)idx[u] * 16, v[u]);
+          if (idx[u] < nvec) v[u] = ld_stream_v4((const char*)p.in + (size_t)idx[u] * 16);
         }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (idx[u] < nvec) st_v4(xin + (size_t)idx[u] * 16, v[u]);
+      }
+      // CTA barrier, then ONE thread fences at system scope (cumulative over what the barrier
+      // ordered before it), counts the CTA in, and the last one raises the flag everywhere
+      __syncthreads();
+      if (threadIdx.x == 0) {
         __threadfence_system();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          const uint32_t prev = atomicAdd(&p.st->nv_arrive[g], 1u);
-          if (prev == (uint32_t)link_blocks - 1u) {
-            p.st->nv_arrive[g] = 0;
-            __threadfence_system();
-            mc_st_release_u32(nv_flag(p.nv_mc, (int)g, p.rank), tag);
-          }
+        const uint32_t prev = atomicAdd(&p.st->nv_arrive[g], 1u);
+        if (prev == (uint32_t)copy_blocks - 1u) {
+          p.st->nv_arrive[g] = 0;
+          __threadfence_system();
+          mc_st_release_u32(nv_flag(p.nv_mc, (int)g, p.rank), tag);
         }
       }
-      if (g >= 1) {
-        const uint32_t gg = g - 1;
-        if (threadIdx.x < world) {
-          const uint32_t* f = reinterpret_cast<const uint32_t*>(nv_flag(p.nv_uc, (int)gg, (int)threadIdx.x));
-          while (ld_acquire_sys(f) != tag)
-            if (sg.expired(p)) break;
+    }
+  }
+  if ((int)blockIdx.x < red_blocks) {
+    // ---- REDUCE: in-switch sum of my chunk, broadcast of the rounded sums, in place.
+    // The CTAs form `teams` teams; team t takes groups t, t + teams, ...  Finishing a slice
+    // costs a drain of the team's multicast stores (system fence) plus an atomic and a flag
+    // store, several microseconds in which that team moves nothing: with the teams on different
+    // groups one team's drain hides behind the others' traffic.
+    const uint32_t teams = (uint32_t)p.nv_teams;
+    const uint32_t rb = blockIdx.x;
+    const uint32_t team = rb % teams, team_size = (uint32_t)p.link_blocks / teams;
+    const uint32_t ltid = (rb / teams) * blockDim.x + threadIdx.x;
+    const uint32_t lsize = team_size * blockDim.x;
+    const uint32_t my0 = (uint32_t)p.rank * chunk;
+    for (uint32_t g = team; g < G; g += teams) {
+      if (threadIdx.x < world) {
+        const uint32_t* f = reinterpret_cast<const uint32_t*>(nv_flag(p.nv_uc, (int)g, (int)threadIdx.x));
+        while ((int32_t)(ld_acquire_sys(f) - tag) < 0)
+          if (sg.expired(p)) break;
+      }
+      __syncthreads();
+      const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk);
+      for (uint32_t base = v0 + ltid; base < v1; base += lsize * U) {
+        uint4 x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint32_t v = base + (uint32_t)u * lsize;
+          x[u] = make_uint4(v, 0, 0, 0);
+          if (v < v1 && my0 + v < nvec && !(p.nv_debug & 2))
+            x[u] = VecOps<T>::mc_ld_reduce(mc_xin + (size_t)(my0 + v) * 16);
         }
-        __syncthreads();
-        const uint32_t v0 = min(gg * sub, chunk), v1 = min(v0 + sub, chunk);
-        const uint32_t my0 = (uint32_t)p.rank * chunk;
-        for (uint32_t base = v0 + ltid; base < v1; base += lsize * U) {
-          uint4 x[U];
 #pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const uint32_t v = base + (uint32_t)u * lsize;
-            if (v < v1 && my0 + v < nvec) x[u] = VecOps<T>::mc_ld_reduce(mc_xin + (size_t)(my0 + v) * 16);
-          }
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const uint32_t v = base + (uint32_t)u * lsize;
-            if (v < v1 && my0 + v < nvec) {
-              scrub(x[u]);
-              mc_st_v4(sum_mc + (size_t)(my0 + v) * 16, x[u]);
-            }
-          }
+        for (int u = 0; u < U; ++u) {
+          const uint32_t v = base + (uint32_t)u * lsize;
+          if (v < v1 && my0 + v < nvec && !(p.nv_debug & 4)) mc_st_v4(mc_xin + (size_t)(my0 + v) * 16, x[u]);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        const uint32_t prev = atomicAdd(&p.st->nv_arrive_red[g], 1u);
+        if (prev == team_size - 1u) {
+          p.st->nv_arrive_red[g] = 0;
+          __threadfence_system();
+          mc_st_release_u32(nv_flag(p.nv_mc + kNvFlagBOff, (int)g, p.rank), tag);
         }
       }
     }
   } else {
-    const int row0 = (int)blockIdx.x - link_blocks;
-    const int row_stride = (int)gridDim.x - link_blocks;
+    // ---- ROW: re-arm what a preceding push call left, then consume the sums slice by slice
+    const int row0 = (int)blockIdx.x - red_blocks;
+    const int row_stride = copy_blocks;
     const size_t rtid = (size_t)row0 * blockDim.x + threadIdx.x;
     const size_t rsize = (size_t)row_stride * blockDim.x;
     rearm_previous(p, pb, rtid, rsize);
-    if (FUSED) {
+    SliceGate gate;
+    if (p.nv_debug & 8) {
+      // measurement only: no consumer
+    } else if (FUSED) {
       int parity = 0;
-      for (int row = row0; row < p.tokens; row += row_stride) {
-        const size_t row_vec0 = (size_t)row * p.hv;
+      const ArrivalOrder order((uint32_t)p.tokens, world, G);
+      for (uint32_t q = (uint32_t)row0; q < order.total; q += (uint32_t)row_stride) {
+        const long long rq = order.at(q);
+        if (rq < 0) continue;
+        const size_t row_vec0 = (size_t)rq * p.hv;
         uint4 s[VPT], res[VPT];
         load_residual<VPT>(res, row_vec0, p);
 #pragma unroll
         for (int j = 0; j < VPT; ++j) {
           const int c = threadIdx.x + j * blockDim.x;
-          if (c < p.hv) s[j] = wait_one(sum_uc + (row_vec0 + c) * 16, p, sg);
+          if (c < p.hv) gate.wait(p, (uint32_t)(row_vec0 + c), chunk, sub, tag, sg);
+        }
+#pragma unroll
+        for (int j = 0; j < VPT; ++j) {
+          const int c = threadIdx.x + j * blockDim.x;
+          if (c < p.hv) s[j] = ld_poll_v4(xin + (row_vec0 + c) * 16);  // L1 may hold last call's line
         }
         row_epilogue<T, VPT>(s, res, gam, row_vec0, p, smem, parity);
       }
     } else {
-      for (size_t idx = rtid; idx < nvec; idx += rsize)
-        st_v4((char*)p.out + idx * 16, wait_one(sum_uc + idx * 16, p, sg));
+      const ArrivalOrder order(nvec, world, G);
+      for (size_t base = rtid; base < order.total; base += rsize * U) {
+        long long idx[U];
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const size_t q = base + (size_t)u * rsize;
+          idx[u] = q < order.total ? order.at((uint32_t)q) : -1;
+          if (idx[u] >= 0) gate.wait(p, (uint32_t)idx[u], chunk, sub, tag, sg);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (idx[u] >= 0) v[u] = ld_poll_v4(xin + idx[u] * 16);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (idx[u] >= 0) st_v4((char*)p.out + idx[u] * 16, v[u]);
+      }
     }
   }
-  end_call(p, cs, 0ull, 0ull, (unsigned long long)nvec * 16);
+  end_call(p, cs, 0ull, 0ull);
 }
 
 template <typename T, int VPT, bool FUSED>
