@@ -111,3 +111,68 @@ def test_real_multi_gpu(world):
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok in res), res
+
+
+def _vllm_worker(rank, world, port, q):
+    """The vLLM-facing layer on real GPUs: plugin.register() -> GroupCoordinator builds a
+    B200Communicator -> tensor_model_parallel_all_reduce / all_gather and the fused custom op."""
+    ok, why = True, ""
+    try:
+        torch.cuda.set_device(rank)
+        from oracle import oracle
+        from vllm.config import VllmConfig, set_current_vllm_config
+        from vllm.distributed import parallel_state as ps
+        from vllm.distributed.communication_op import (tensor_model_parallel_all_gather,
+                                                       tensor_model_parallel_all_reduce)
+        from vllm_distributed_b200 import plugin
+        from vllm_distributed_b200.communicator import B200Communicator
+        plugin.register()
+        with set_current_vllm_config(VllmConfig()):
+            ps.init_distributed_environment(world_size=world, rank=rank, local_rank=rank,
+                                            distributed_init_method=f"tcp://127.0.0.1:{port}",
+                                            backend="nccl")
+            ps.initialize_model_parallel(world, 1)
+            tp = ps.get_tp_group()
+            comm = tp.device_communicator
+            assert isinstance(comm, B200Communicator) and comm.b200 is not None, type(comm)
+            for t, h in [(1, 4096), (64, 8192), (300, 4096)]:
+                xs = [torch.randn(t, h, generator=torch.Generator().manual_seed(1234 + r)).bfloat16()
+                      for r in range(world)]
+                res = torch.randn(t, h, generator=torch.Generator().manual_seed(7)).bfloat16()
+                gamma = torch.randn(h, generator=torch.Generator().manual_seed(8)).bfloat16()
+                y_ref, r_ref, ar_ref = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+                ar = tensor_model_parallel_all_reduce(xs[rank].cuda())
+                xd, rd = xs[rank].cuda(), res.cuda()
+                torch.ops.vllm.b200c_allreduce_add_rmsnorm(xd, rd, gamma.cuda(), 1e-5, tp.unique_name)
+                torch.cuda.synchronize()
+                ok &= torch.equal(ar.cpu(), ar_ref) and torch.equal(rd.cpu(), r_ref)
+                ok &= bool(torch.allclose(xd.cpu().float(), y_ref.float(), atol=1e-3, rtol=1.6e-2))
+            slabs = [torch.randn(5, 1024, generator=torch.Generator().manual_seed(50 + r)).bfloat16()
+                     for r in range(world)]
+            full = tensor_model_parallel_all_gather(slabs[rank].cuda(), -1)
+            ok &= torch.equal(full.cpu(), oracle.all_gather_lastdim(slabs))
+            comm.check_health()
+            torch.distributed.barrier()
+        ps.destroy_model_parallel()
+        ps.destroy_distributed_environment()
+    except Exception:  # noqa: BLE001
+        import traceback
+        ok, why = False, traceback.format_exc()[-1500:]
+    q.put((rank, bool(ok), why))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_vllm_communicator_api_on_real_gpus(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_vllm_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res

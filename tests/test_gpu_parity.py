@@ -407,6 +407,33 @@ def test_auto_falls_back_to_two_shot_when_one_shot_does_not_fit(pkg):
     g.check_health()
 
 
+@pytest.mark.parametrize("world", [3, 5, 6, 7])
+def test_odd_group_sizes_at_exactly_max_bytes(pkg, world):
+    """Group sizes that do not divide the message: a two-shot call rounds the message up to
+    `world` equal chunks of whole vectors, and the arena halves carry that slack, so a message of
+    exactly max_bytes must fit (it used to be rejected with B200C_ETOOBIG)."""
+    comm, emu, C = pkg
+    max_bytes = 64 * 1024 + 16 * 13   # not a multiple of 16 * world for any of these worlds
+    g = group(pkg, world, max_bytes=max_bytes, ag_bytes=1 << 20, p2p_bytes=1 << 20)
+    assert g.ranks[0].can_all_reduce(torch.empty(max_bytes // 2, dtype=torch.bfloat16, device="cuda"))
+    xs = [rand((max_bytes // 2,), torch.bfloat16, 300 + r) for r in range(world)]
+    ref = oracle.all_reduce(xs)
+    for variant in (C.TWOSHOT, C.AUTO):
+        for o in g.all_reduce([x.cuda() for x in xs], variant=variant):
+            assert bits_equal(o, ref)
+    # fused, rows of 13 vectors: 4096 + 13 = 4109 vectors do not divide either
+    t, h = (max_bytes // 16) // 13, 13 * 8
+    xs = [rand((t, h), torch.bfloat16, 400 + r) for r in range(world)]
+    res, gamma = rand((t, h), torch.bfloat16, 7), rand((h,), torch.bfloat16, 8)
+    y_ref, r_ref, _ = oracle.all_reduce_add_rms_norm(xs, res, gamma, 1e-5)
+    ys, rs = g.all_reduce_add_rmsnorm([x.cuda() for x in xs], [res.cuda() for _ in range(world)],
+                                      gamma.cuda(), 1e-5, variant=C.TWOSHOT)
+    for r in range(world):
+        assert bits_equal(rs[r], r_ref)
+    check_norm(ys[0], y_ref, torch.bfloat16)
+    g.check_health()
+
+
 def test_full_size_properties(pkg):
     """BASELINE sweep maximum (8192 tokens x 8192 hidden, bf16 = 128 MiB): too slow for the CPU
     oracle in a unit test, so check size-independent properties instead."""

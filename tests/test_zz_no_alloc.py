@@ -77,3 +77,17 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row():
     assert _call_noalloc(C, eight, [torch.empty_like(b) for b in eight], C.TWOSHOT) == C.OK
     torch.cuda.synchronize()
     ref_group.close()
+
+    # three ranks at exactly the 64 KiB limit: 4096 vectors do not divide by 3, the two-shot
+    # chunks are rounded up -- the static array carries that slack, so the documented limit holds
+    ref3 = EmuGroup(3, "cuda:0", max_bytes=1 << 20, ag_bytes=1 << 20, p2p_bytes=1 << 20)
+    ref3.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, 3000)
+    xs3 = [torch.randn(C.NOALLOC_MAX_BYTES // 2, generator=gen).bfloat16().cuda() for _ in range(3)]
+    outs3 = [torch.empty_like(x) for x in xs3]
+    want3 = ref3.all_reduce(xs3, variant=C.TWOSHOT)
+    for variant in (C.TWOSHOT, C.AUTO):
+        C.check(_call_noalloc(C, xs3, outs3, variant))
+        torch.cuda.synchronize()
+        for r in range(3):
+            assert torch.equal(outs3[r].view(torch.uint8), want3[r].view(torch.uint8)), f"3 ranks, rank {r}"
+    ref3.close()

@@ -71,7 +71,11 @@ def main():
     os.environ.setdefault("VLLM_LOGGING_LEVEL", "INFO")
     fi_aot = os.path.join(ROOT, "baseline", "_fi", "aot")
     if os.path.isdir(fi_aot):
-        os.environ["B200C_FLASHINFER_AOT_DIR"] = fi_aot
+        # the stock comparator's FlashInfer module, cross-compiled ahead of time (bench infrastructure)
+        shim = os.path.join(ROOT, "tools", "fi_jit_cache_shim")
+        os.environ["PYTHONPATH"] = shim + os.pathsep + os.environ["PYTHONPATH"]
+        os.environ["FLASHINFER_DISABLE_VERSION_CHECK"] = "1"
+        sys.path.insert(0, shim)
 
     import random
     from vllm import LLM, SamplingParams

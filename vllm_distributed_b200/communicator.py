@@ -135,7 +135,8 @@ class B200Communicator(CudaCommunicator):
         if dst is None:
             dst = (self.rank_in_group + 1) % self.world_size
         b = self.b200
-        if b is not None and tensor.is_cuda and (tensor.numel() * tensor.element_size()) % 16 == 0:
+        if (b is not None and tensor.device.type == self.device.type
+                and (tensor.numel() * tensor.element_size()) % 16 == 0):
             # the receiver decides by the byte count alone (it allocates an aligned tensor), so
             # the sender must too: a strided or misaligned source is copied, not re-routed
             if not tensor.is_contiguous() or tensor.data_ptr() % 16:

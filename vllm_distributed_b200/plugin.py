@@ -59,23 +59,56 @@ def _patch_platform() -> None:
         return  # CPU / other platforms keep their own communicator
     cls.get_device_communicator_cls = classmethod(lambda c: COMM_QUALNAME)
     cls._b200c_patched = True
+    # the TP=1 seam: libb200c's norm kernels as an IR-op provider, ahead of vLLM's own C kernels
+    from . import norm_provider
+    if norm_provider.register():
+        norm_provider.prioritise(cls)
 
 
-def _use_prebuilt_flashinfer() -> None:
-    """Benchmark convenience: let the stock FlashInfer comparator load a module that was
-    cross-compiled ahead of time (baseline/_fi/aot) instead of JIT-compiling for minutes."""
-    aot = os.environ.get("B200C_FLASHINFER_AOT_DIR")
-    if aot and os.path.isdir(aot):
-        import pathlib
-        from flashinfer.jit import env as jit_env
-        jit_env.FLASHINFER_AOT_DIR = pathlib.Path(aot)
+def _hook_worker_health() -> None:
+    """The reference launcher polls `check_health` on every worker (launch.py:386-388); make that
+    call read the sticky device-side error word of every b200c communicator, so that a timed-out
+    wait on a peer fails the health check instead of going unnoticed."""
+    try:
+        from vllm.v1.worker.worker_base import WorkerBase
+    except Exception:  # noqa: BLE001
+        return
+    if getattr(WorkerBase, "_b200c_health_hooked", False):
+        return
+
+    def _check_groups() -> None:
+        from vllm.distributed import parallel_state as ps
+        for getter in ("get_tp_group", "get_pp_group"):
+            try:
+                comm = getattr(ps, getter)().device_communicator
+            except Exception:  # noqa: BLE001 -- group not initialised (yet)
+                continue
+            if comm is not None and hasattr(comm, "check_health"):
+                comm.check_health()   # raises B200CError(ETIMEOUT) -> the RPC reports a failed worker
+
+    def wrap(cls) -> None:
+        orig = cls.__dict__.get("check_health")
+        if orig is None:
+            return
+
+        def check_health(self, *a, **k):
+            _check_groups()
+            return orig(self, *a, **k)
+        cls.check_health = check_health
+
+    wrap(WorkerBase)
+    try:
+        from vllm.v1.worker.gpu_worker import Worker
+        wrap(Worker)
+    except Exception:  # noqa: BLE001 -- CPU-only install
+        pass
+    WorkerBase._b200c_health_hooked = True
 
 
 def register() -> None:
     global _DONE
     if _DONE:
         return
-    _use_prebuilt_flashinfer()
     if os.environ.get("B200C_DISABLE", "0") == "1":
         return
     _DONE = True
@@ -89,3 +122,7 @@ def register() -> None:
     if os.environ.get("B200C_PP_CHANNEL", "1") == "1":
         from . import pp_channel
         pp_channel.apply()
+    if os.environ.get("B200C_FUSION_PASS", "1") == "1":
+        from . import fusion_pass
+        fusion_pass.install_in_pass_manager()
+    _hook_worker_health()
