@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -417,11 +418,48 @@ int launch_ar_t(b200c_ctx* const* ctxs, int nemu, const RankParams* rp, int want
   return launch(ar_kernel_emu<T, TWOSHOT>, dim3(g, nemu, 1), threads, ep, s, true);
 }
 
+// Tuning aid (tools/norm_sweep.py): B200C_NORM_VARIANT = rows | small2 | small4 | small8
+// forces one bandwidth-regime kernel; unset = the measured choice below.
+int norm_variant_override() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200C_NORM_VARIANT");
+    v = 0;
+    if (e) {
+      if (!strcmp(e, "rows")) v = 1;
+      else if (!strcmp(e, "small2")) v = 3;
+      else if (!strcmp(e, "small4")) v = 4;
+      else if (!strcmp(e, "small8")) v = 5;
+    }
+  }
+  return v;
+}
+
 template <typename T>
 int launch_norm_only(const RankParams& rp, int vpt, int threads, int sm_count, cudaStream_t s,
                      bool pdl) {
-  if (vpt == 1 && rp.tokens >= 8 * sm_count) {
-    // bandwidth regime with narrow rows: four rows per trip (see norm_kernel_rows)
+  const int force = norm_variant_override();
+  const bool bw = rp.tokens >= 8 * sm_count;  // every SM has several rows of work
+  // Many small CTAs, one row each (tools/norm_sweep.py, profiles/r2_norm_sweep_tp1.json): rows of
+  // up to 512 vectors from two rows per SM upwards, wider rows once every SM has eight.  The grid
+  // is one CTA per row: capping it and looping cost 3-4 % at 16384 rows (wave tails).
+  const bool small_ok = rp.hv % 64 == 0 && rp.hv <= 2048 &&
+                        (rp.hv <= 512 ? rp.tokens >= 2 * sm_count : bw);
+  if (small_ok && (force == 0 || (force >= 3 && force <= 5))) {
+    int v = force == 3 ? 2 : force == 4 ? 4 : force == 5 ? 8 : (rp.hv <= 512 ? 2 : rp.hv <= 1024 ? 4 : 8);
+    while (rp.hv / v > 256) v *= 2;
+    const int t = rp.hv / v;
+    if (v <= 8 && t % 32 == 0) {
+      const int g = std::max(1, rp.tokens);
+      switch (v) {
+        case 2: return launch(norm_kernel_small<T, 2, 6>, dim3(g, 1, 1), t, rp, s, false, pdl);
+        case 4: return launch(norm_kernel_small<T, 4, 5>, dim3(g, 1, 1), t, rp, s, false, pdl);
+        case 8: return launch(norm_kernel_small<T, 8, 3>, dim3(g, 1, 1), t, rp, s, false, pdl);
+      }
+    }
+  }
+  if (vpt == 1 && bw) {
+    // narrow rows: four rows per trip (see norm_kernel_rows)
     const int g = std::max(1, std::min((rp.tokens + 3) / 4, sm_count * 8));
     return launch(norm_kernel_rows<T, 4>, dim3(g, 1, 1), threads, rp, s, false, pdl);
   }

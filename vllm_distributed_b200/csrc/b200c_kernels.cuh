@@ -1124,6 +1124,75 @@ __global__ void __launch_bounds__(512, 2) norm_kernel_rows(const __grid_constant
   }
 }
 
+// Bandwidth regime, many small CTAs: a row on blockDim = hv / VPT <= 256 threads, MINB resident
+// CTAs per SM.  Nothing is pipelined inside a CTA; instead the SM holds many independent CTAs
+// whose barriers (over 4-8 warps only) fall at different times, so the memory system always sees
+// loads from some of them.  Registers are kept low for that residency: only the raw vectors
+// live across the barrier, x = s + r is recomputed and gamma re-read (an L1 hit) afterwards.
+// (Tried and dropped, profiles/r2_norm_sweep_variants.json: a software-pipelined 512-thread kernel
+// that issues the next trip's loads before the barrier, 3-6 % slower; a 29-register kernel that
+// reads each row twice so that eight CTAs per SM are resident, 5-30 % slower.)
+// Same per-row arithmetic and reduction tree as norm_kernel, hence the same bits.
+template <typename T, int VPT, int MINB>
+__global__ void __launch_bounds__(256, MINB) norm_kernel_small(const __grid_constant__ RankParams p) {
+  constexpr int EPV = VecOps<T>::EPV;
+  __shared__ float smem[64];
+  pdl_launch_dependents();
+  pdl_wait();
+  int parity = 0;
+  const bool has_res = p.res_in != nullptr;
+  for (int row = blockIdx.x; row < p.tokens; row += gridDim.x) {
+    const size_t row_vec0 = (size_t)row * p.hv;
+    uint4 s[VPT], r[VPT];
+#pragma unroll
+    for (int j = 0; j < VPT; ++j) {
+      const int c = threadIdx.x + j * blockDim.x;
+      if (c < p.hv) {
+        s[j] = ld_stream_v4((const char*)p.in + (row_vec0 + c) * 16);
+        if (has_res) r[j] = ld_stream_v4((const char*)p.res_in + (row_vec0 + c) * 16);
+      }
+    }
+    float ss = 0.0f;
+#pragma unroll
+    for (int j = 0; j < VPT; ++j) {
+      const int c = threadIdx.x + j * blockDim.x;
+      if (c < p.hv) {
+        float x[EPV];
+        VecOps<T>::to_float(s[j], x);
+        if (has_res) {
+          float rr[EPV];
+          VecOps<T>::to_float(r[j], rr);
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) x[e] = x[e] + rr[e];
+          st_v4((char*)p.res_out + (row_vec0 + c) * 16, VecOps<T>::from_float(x));
+        }
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) ss += x[e] * x[e];
+      }
+    }
+    const float total = block_sum(ss, smem, parity);
+    const float rs = 1.0f / sqrtf(total / (float)p.hidden + p.eps);
+#pragma unroll
+    for (int j = 0; j < VPT; ++j) {
+      const int c = threadIdx.x + j * blockDim.x;
+      if (c < p.hv) {
+        float x[EPV], g[EPV], y[EPV];
+        VecOps<T>::to_float(s[j], x);
+        if (has_res) {
+          float rr[EPV];
+          VecOps<T>::to_float(r[j], rr);
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) x[e] = x[e] + rr[e];
+        }
+        VecOps<T>::to_float(ld_v4((const char*)p.gamma + (size_t)c * 16), g);
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) y[e] = VecOps<T>::round_trip(x[e] * rs) * g[e];
+        st_v4((char*)p.norm_out + (row_vec0 + c) * 16, VecOps<T>::from_float(y));
+      }
+    }
+  }
+}
+
 // ---- all-gather along the last dim (byte-exact; flag protocol) -----------------------------------
 // Staging layout in every rank's arena = the final [rows][world][row_bytes] layout, double
 // buffered on the call parity.  Each rank pushes its slab into all peers' staging, fences,
