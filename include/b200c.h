@@ -61,11 +61,11 @@ extern "C" {
 #define B200C_TUNE_TRAP_ON_TIMEOUT 10  /* 0 (default): a timed-out wait sets the sticky error word; 1: it also \
                                           executes `trap`, so the next CUDA call of the process fails    */
 
-#define B200C_TUNE_NVLS_MIN_BYTES 11   /* AUTO picks NVLS at or above this size; < 0 (default) = never  */
+#define B200C_TUNE_NVLS_MIN_BYTES 11   /* AUTO picks NVLS at or above this size; < 0 = never (default: 48 MiB at 8 ranks, never below) */
 #define B200C_TUNE_NVLS_LINK_BLOCKS 12 /* NVLS CTAs doing the in-switch reduce + broadcast; 0 = grid/6    */
-#define B200C_TUNE_NVLS_GROUPS 13      /* NVLS copy-in pipeline groups (1..8); 0 = by size               */
-#define B200C_TUNE_NVLS_COPY_BLOCKS 14 /* NVLS CTAs copying the input into the symmetric buffer; 0 = grid/6 */
-#define B200C_TUNE_NVLS_TEAMS 15       /* NVLS reduce CTAs work in this many teams (1..8), each on its own group; 0 = 4 */
+#define B200C_TUNE_NVLS_GROUPS 13      /* NVLS pipeline groups (1..14); 0 = by size (one per 8 MiB, <= 8) */
+#define B200C_TUNE_NVLS_COPY_BLOCKS 14 /* retired (every non-reduce CTA copies in, then consumes): accepted, ignored */
+#define B200C_TUNE_NVLS_TEAMS 15       /* NVLS reduce CTAs work in this many teams (1..14), each on its own group; 0 = one per group */
 #define B200C_TUNE_NVLS_DEBUG 16       /* measurement only, results are garbage: 1 no copy-in, 2 no ld_reduce, \
                                           4 no multimem.st, 8 no consumer */
 

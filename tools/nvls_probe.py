@@ -74,13 +74,11 @@ def main():
         rows.append({"tokens": T, "label": "push two-shot", "us": round(us2, 2)})
         run(T, "default")
         run(T, "default, plain all-reduce", plain=True)
-        for teams in (1, 2, 4, 8):
-            run(T, f"teams {teams}", teams=teams)
-        for groups in (1, 2, 4, 8):
-            run(T, f"groups {groups}", groups=groups)
-        for red in (16, 24, 32, 48, 64, 96):
-            run(T, f"reduce CTAs {red}", red=red)
-        for red, teams, groups in ((32, 8, 8), (48, 8, 8), (32, 2, 4), (48, 4, 4), (24, 2, 2)):
+        for groups in (2, 4, 8, 14):
+            for teams in (1, 2, 4, 7):
+                if teams <= groups:
+                    run(T, f"groups {groups} teams {teams}", groups=groups, teams=teams)
+        for red, teams, groups in ((24, 2, 14), (48, 2, 14), (48, 4, 14), (64, 4, 14), (56, 7, 14), (48, 8, 8)):
             run(T, f"reduce CTAs {red} teams {teams} groups {groups}", red=red, teams=teams, groups=groups)
         for dbg, what in ((1, "no copy-in"), (8, "no consumer"), (9, "no copy-in, no consumer"),
                           (4, "no multimem.st (+ consumer off)"), (2, "no ld_reduce"),

@@ -86,7 +86,7 @@ struct b200c_ctx {
   int nvls_link_blocks = 0;       // reduce CTAs; 0 = a sixth of the grid
   int nvls_copy_blocks = 0;       // copy-in CTAs; 0 = a sixth of the grid
   int nvls_groups = 0;            // copy-in pipeline groups; 0 = by size
-  int nvls_teams = 0;             // reduce teams; 0 = 4
+  int nvls_teams = 0;             // reduce teams; 0 = one per group
   int nvls_debug = 0;             // measurement only: phase-skipping bits
 };
 
@@ -354,10 +354,10 @@ int launch_ar_norm_cluster(b200c_ctx* const* ctxs, int nemu, const RankParams* r
 // ---- NVLS variant (real ranks only: a multicast group has one member per device) -------------
 int nvls_groups_for(const b200c_ctx* c, size_t bytes) {
   if (c->nvls_groups > 0) return std::min(c->nvls_groups, kNvMaxGroups);
-  // Every group costs each copy CTA a system fence, an atomic and (the last one) a multicast
-  // flag store -- about 12 us per group measured on 8 x B200 (tools/nvls_probe.py) -- so groups
-  // only pay when a group's link time is well above that: one per 16 MiB, at most 4.
-  return (int)std::max<size_t>(1, std::min<size_t>(4, bytes >> 24));
+  // One pipeline group per 8 MiB, at most 8 (tools/nvls_probe.py on 8 x B200, profiles/
+  // r2_nvls_probe_tp8_f.json): finer groups shorten the consumers' tail but every group costs the
+  // reduce side a drain of its multicast stores; 8 groups x 8 teams was the best point at 64 MiB.
+  return (int)std::max<size_t>(1, std::min<size_t>(8, bytes >> 23));
 }
 
 template <typename K>
@@ -367,12 +367,13 @@ int launch_nvls_k(K kernel, b200c_ctx* c, RankParams p, size_t bytes, cudaStream
   int rc = coresident_blocks(kernel, threads, c->sm_count, &cap);
   if (rc) return rc;
   const int g = std::max(2, std::min(twoshot_grid(c, bytes), cap));
-  // roles (tools/nvls_bench.cu): about an eighth of the grid saturates the link on the reduce
-  // side (more CTAs only add contention); every other CTA copies in and then consumes
+  // roles (tools/nvls_bench.cu, tools/nvls_probe.py): about a sixth of the grid saturates the
+  // link on the reduce side (more CTAs only add contention); every other CTA copies in and
+  // then consumes
   p.nv_groups = nvls_groups_for(c, bytes);
-  int red = c->nvls_link_blocks > 0 ? c->nvls_link_blocks : std::max(1, g / 8);
+  int red = c->nvls_link_blocks > 0 ? c->nvls_link_blocks : std::max(1, g / 6);
   red = std::max(1, std::min(red, g - 1));
-  int teams = c->nvls_teams > 0 ? c->nvls_teams : 4;
+  int teams = c->nvls_teams > 0 ? c->nvls_teams : p.nv_groups;  // every group has its own team
   teams = std::max(1, std::min(teams, std::min(p.nv_groups, red)));
   red = red / teams * teams;  // equal teams
   p.link_blocks = red;
@@ -800,6 +801,11 @@ int b200c_attach_nvls(b200c_ctx* c, void* uc_ptr, void* mc_ptr, size_t bytes) {
   c->nv_uc = uc;
   c->nv_mc = static_cast<char*>(mc_ptr);
   c->nv_half = half;
+  // AUTO: measured on 8 x B200 (profiles/r2_sweep_tp8_h8192_final.json) the in-switch variant wins
+  // from 64 MiB upwards at 8 ranks (194 us vs 215 us) and loses below; at 2 ranks it moves MORE
+  // bytes than the push kernels and at 4 it was not measured to win, so it stays opt-in there
+  // (B200C_TUNE_NVLS_MIN_BYTES).  It is tolerance-parity, not bit-parity (see nvls_body).
+  if (c->nvls_min_bytes < 0 && c->world >= 8) c->nvls_min_bytes = 48ll << 20;
   return B200C_OK;
 }
 
@@ -1140,7 +1146,7 @@ namespace {
 constexpr size_t kNoAllocMaxBytes = 64 * 1024;
 constexpr size_t kNoAllocHalf = kNoAllocMaxBytes + 256;  // make_geom's half for this max_bytes (chunk-rounding slack)
 constexpr size_t kNoAllocArenaBytes = kCtrlBytes + 3 * 2 * kNoAllocHalf + 2 * 256 + kMaxRanks * 2 * 256;
-constexpr size_t kNoAllocStateStride = 256;
+constexpr size_t kNoAllocStateStride = 512;
 static_assert(sizeof(LocalState) <= kNoAllocStateStride, "LocalState must fit its slot");
 constexpr size_t kNoAllocStateOff = kMaxRanks * kNoAllocArenaBytes;
 constexpr size_t kNoAllocScratchBytes = kNoAllocStateOff + kMaxRanks * kNoAllocStateStride;

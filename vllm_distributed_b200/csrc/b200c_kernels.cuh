@@ -42,8 +42,8 @@ struct LocalState {
   uint32_t send_seq[kMaxRanks];
   uint32_t recv_seq[kMaxRanks];
   // NVLS variant: CTA arrival counters of the copy-in groups and of the reduce slices
-  uint32_t nv_arrive[8];
-  uint32_t nv_arrive_red[8];
+  uint32_t nv_arrive[16];
+  uint32_t nv_arrive_red[16];
 };
 
 struct RankParams {
@@ -157,16 +157,16 @@ __device__ __forceinline__ void rearm(char* base, unsigned long long bytes, size
 
 
 // ---- NVLS buffer layout (bytes from its base; identical on every rank) ---------------------------
-// [0, 16K)       flagA [8 groups][8 src], one per 128-byte line: flagA[g][r] = epoch+1 of the last
+// [0, 16K)       flagA [16 groups][8 src], one per 128-byte line: flagA[g][r] = epoch+1 of the last
 //                call in which rank r has finished copying group g of its input into xin
-// [16K, 32K)     flagB [8 groups][8 owner]: flagB[g][o] = epoch+1 of the last call in which owner o
+// [16K, 32K)     flagB [16 groups][8 owner]: flagB[g][o] = epoch+1 of the last call in which owner o
 //                has broadcast the sums of slice g of its chunk
 //                (both are written through the multicast mapping: one store updates every rank)
 // 1 x nv_half    xin: this rank's input, copied in so that the switch can read it; the sums are
 //                written back IN PLACE (by multicast) and consumed from here
 constexpr size_t kNvCtrlBytes = 32 * 1024;
 constexpr size_t kNvFlagBOff = 16 * 1024;
-constexpr int kNvMaxGroups = 8;
+constexpr int kNvMaxGroups = 14;  // one named barrier id (1 + g) per group, ids 1..14
 
 __device__ __forceinline__ char* nv_flag(char* base, int group, int src) {
   return base + ((size_t)group * kMaxRanks + src) * kFlagStride;
@@ -827,18 +827,38 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
 // rounds ties differently from round-to-nearest-even and its summation order is unspecified, so
 // this variant is tolerance-parity with the oracle (north_star's 1e-2), never bit-parity; all
 // ranks still get identical bits because each sum is computed once and broadcast.
+// Consumers wait per CTA, not per thread: ONE thread polls the slice's flag (with a short sleep
+// between polls) and the CTA barrier hands the result to the others.  Every thread polling the
+// same few flag lines with system-scope acquires (130 k threads on 64 lines) slowed the whole
+// kernel down by a third (tools/nvls_probe.py: 169 us without consumers, 242 us with).
 struct SliceGate {
-  uint32_t seen = 0xffffffffu;  // slice id this thread has already found complete
+  uint32_t seen_a = 0xffffffffu, seen_b = 0xffffffffu;  // slice ids this CTA has found complete
   template <typename P>
-  __device__ __forceinline__ void wait(const P& p, uint32_t idx, uint32_t chunk, uint32_t sub,
-                                       uint32_t tag, SpinGuard& sg) {
-    const uint32_t o = idx / chunk, g = (idx - o * chunk) / sub;
-    const uint32_t id = g * kMaxRanks + o;
-    if (id == seen) return;
-    const uint32_t* f = reinterpret_cast<const uint32_t*>(nv_flag(p.nv_uc + kNvFlagBOff, (int)g, (int)o));
-    while ((int32_t)(ld_acquire_sys(f) - tag) < 0)
+  static __device__ __forceinline__ void poll(const P& p, uint32_t id, uint32_t tag, SpinGuard& sg) {
+    const uint32_t* f = reinterpret_cast<const uint32_t*>(
+        nv_flag(p.nv_uc + kNvFlagBOff, (int)(id / kMaxRanks), (int)(id % kMaxRanks)));
+    while ((int32_t)(ld_acquire_sys(f) - tag) < 0) {
+      __nanosleep(64);
       if (sg.expired(p)) break;
-    seen = id;
+    }
+  }
+  static __device__ __forceinline__ uint32_t slice_of(uint32_t idx, uint32_t chunk, uint32_t sub) {
+    const uint32_t o = idx / chunk, g = (idx - o * chunk) / sub;
+    return g * kMaxRanks + o;
+  }
+  // all threads of the CTA call this with the same arguments (vector range [first, last])
+  template <typename P>
+  __device__ __forceinline__ void wait(const P& p, uint32_t first, uint32_t last, uint32_t chunk,
+                                       uint32_t sub, uint32_t tag, SpinGuard& sg) {
+    const uint32_t a = slice_of(first, chunk, sub), b = slice_of(last, chunk, sub);
+    if ((a == seen_a || a == seen_b) && (b == seen_a || b == seen_b)) return;
+    if (threadIdx.x == 0) {
+      poll(p, a, tag, sg);
+      if (b != a) poll(p, b, tag, sg);
+    }
+    __syncthreads();
+    seen_a = a;
+    seen_b = b;
   }
 };
 
@@ -866,39 +886,49 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
   constexpr int U = 4;
 
   if ((int)blockIdx.x >= red_blocks) {
-    // ---- COPY: sub-slice g of EVERY rank's chunk, group after group
-    const uint32_t ctid = (blockIdx.x - red_blocks) * blockDim.x + threadIdx.x;
-    const uint32_t csize = (uint32_t)copy_blocks * blockDim.x;
+    // ---- COPY: sub-slice g of EVERY rank's chunk, group after group.
+    // The last warp of the CTA does not copy: it is the SIGNAL warp.  The copy warps only
+    // ARRIVE on a named barrier when their part of a group is stored and go straight on to the
+    // next group; the signal warp waits on that barrier, fences (cumulative over what the
+    // barrier ordered before it), counts the CTA in, and the last CTA's signal warp raises the
+    // flag on every rank.  The fence + atomic + flag chain (several microseconds per group,
+    // tools/nvls_probe.py) is thereby off the copy path.  One barrier id per group (1 + g <= 8).
+    const uint32_t cthreads = blockDim.x - 32;
+    const bool is_signal = threadIdx.x >= cthreads;
+    const uint32_t ctid = (blockIdx.x - red_blocks) * cthreads + threadIdx.x;
+    const uint32_t csize = (uint32_t)copy_blocks * cthreads;
     for (uint32_t g = 0; g < G; ++g) {
-      const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk), n = v1 - v0;
-      const uint32_t total = (p.nv_debug & 1) ? 0u : n * world;
-      for (uint32_t base = ctid; base < total; base += csize * U) {
-        uint4 v[U];
-        uint32_t idx[U];
+      if (!is_signal) {
+        const uint32_t v0 = min(g * sub, chunk), v1 = min(v0 + sub, chunk), n = v1 - v0;
+        const uint32_t total = (p.nv_debug & 1) ? 0u : n * world;
+        for (uint32_t base = ctid; base < total; base += csize * U) {
+          uint4 v[U];
+          uint32_t idx[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const uint32_t i = base + (uint32_t)u * csize;
-          idx[u] = nvec;
-          if (i < total) {
-            const uint32_t o = i / n;
-            idx[u] = o * chunk + v0 + (i - o * n);
+          for (int u = 0; u < U; ++u) {
+            const uint32_t i = base + (uint32_t)u * csize;
+            idx[u] = nvec;
+            if (i < total) {
+              const uint32_t o = i / n;
+              idx[u] = o * chunk + v0 + (i - o * n);
+            }
+            if (idx[u] < nvec) v[u] = ld_stream_v4((const char*)p.in + (size_t)idx[u] * 16);
           }
-          if (idx[u] < nvec) v[u] = ld_stream_v4((const char*)p.in + (size_t)idx[u] * 16);
-        }
 #pragma unroll
-        for (int u = 0; u < U; ++u)
-          if (idx[u] < nvec) st_v4(xin + (size_t)idx[u] * 16, v[u]);
-      }
-      // CTA barrier, then ONE thread fences at system scope (cumulative over what the barrier
-      // ordered before it), counts the CTA in, and the last one raises the flag everywhere
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        __threadfence_system();
-        const uint32_t prev = atomicAdd(&p.st->nv_arrive[g], 1u);
-        if (prev == (uint32_t)copy_blocks - 1u) {
-          p.st->nv_arrive[g] = 0;
-          __threadfence_system();
-          mc_st_release_u32(nv_flag(p.nv_mc, (int)g, p.rank), tag);
+          for (int u = 0; u < U; ++u)
+            if (idx[u] < nvec) st_v4(xin + (size_t)idx[u] * 16, v[u]);
+        }
+        named_bar_arrive(1 + g, blockDim.x);
+      } else {
+        named_bar_sync(1 + g, blockDim.x);
+        if (threadIdx.x == cthreads) {
+          __threadfence();  // the copies are local stores: device scope orders them before the count
+          const uint32_t prev = atomicAdd(&p.st->nv_arrive[g], 1u);
+          if (prev == (uint32_t)copy_blocks - 1u) {
+            p.st->nv_arrive[g] = 0;
+            __threadfence();
+            mc_st_release_u32(nv_flag(p.nv_mc, (int)g, p.rank), tag);  // release at system scope
+          }
         }
       }
     }
@@ -908,10 +938,14 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
     // The CTAs form `teams` teams; team t takes groups t, t + teams, ...  Finishing a slice
     // costs a drain of the team's multicast stores (system fence) plus an atomic and a flag
     // store, several microseconds in which that team moves nothing: with the teams on different
-    // groups one team's drain hides behind the others' traffic.
+    // groups one team's drain hides behind the others' traffic.  (A signal warp, as on the copy
+    // side, was tried here and lost: a system fence issued while the CTA's other warps keep
+    // storing through the switch stalls them too -- 287 us instead of 169 us for 64 MiB.)
+    // With few teams and many groups the slices still complete roughly in order, which is what
+    // the consumers, walking the slices in that order, need to stay close behind.
     const uint32_t teams = (uint32_t)p.nv_teams;
     const uint32_t rb = blockIdx.x;
-    const uint32_t team = rb % teams, team_size = (uint32_t)p.link_blocks / teams;
+    const uint32_t team = rb % teams, team_size = (uint32_t)red_blocks / teams;
     const uint32_t ltid = (rb / teams) * blockDim.x + threadIdx.x;
     const uint32_t lsize = team_size * blockDim.x;
     const uint32_t my0 = (uint32_t)p.rank * chunk;
@@ -940,11 +974,11 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
       }
       __syncthreads();
       if (threadIdx.x == 0) {
-        __threadfence_system();
+        __threadfence_system();  // this CTA's multicast stores are performed everywhere
         const uint32_t prev = atomicAdd(&p.st->nv_arrive_red[g], 1u);
         if (prev == team_size - 1u) {
           p.st->nv_arrive_red[g] = 0;
-          __threadfence_system();
+          __threadfence();
           mc_st_release_u32(nv_flag(p.nv_mc + kNvFlagBOff, (int)g, p.rank), tag);
         }
       }
@@ -968,11 +1002,7 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
         const size_t row_vec0 = (size_t)rq * p.hv;
         uint4 s[VPT], res[VPT];
         load_residual<VPT>(res, row_vec0, p);
-#pragma unroll
-        for (int j = 0; j < VPT; ++j) {
-          const int c = threadIdx.x + j * blockDim.x;
-          if (c < p.hv) gate.wait(p, (uint32_t)(row_vec0 + c), chunk, sub, tag, sg);
-        }
+        gate.wait(p, (uint32_t)row_vec0, (uint32_t)(row_vec0 + p.hv - 1), chunk, sub, tag, sg);
 #pragma unroll
         for (int j = 0; j < VPT; ++j) {
           const int c = threadIdx.x + j * blockDim.x;
@@ -981,19 +1011,28 @@ __device__ __forceinline__ void nvls_body(const RankParams& p, float* smem) {
         row_epilogue<T, VPT>(s, res, gam, row_vec0, p, smem, parity);
       }
     } else {
+      // tiles of blockDim * U consecutive positions of the arrival order; a tile lies in one
+      // slice or straddles two neighbouring ones (tiny messages: more -- then every run it
+      // touches is waited for, one by one)
       const ArrivalOrder order(nvec, world, G);
-      for (size_t base = rtid; base < order.total; base += rsize * U) {
+      const uint32_t tile = blockDim.x * U;
+      for (uint32_t t0 = (uint32_t)row0 * tile; t0 < order.total; t0 += (uint32_t)row_stride * tile) {
+        const uint32_t t1 = min(t0 + tile, order.total) - 1;
+        for (uint32_t run = t0 / order.per_slice; run <= t1 / order.per_slice; ++run) {
+          const uint32_t g = run / world, o = run - g * world;
+          const uint32_t within = g * order.per_slice;
+          if (within >= order.per_chunk || o * order.per_chunk + within >= nvec) continue;
+          const uint32_t idx = o * order.per_chunk + within;
+          gate.wait(p, idx, idx, chunk, sub, tag, sg);
+        }
         long long idx[U];
         uint4 v[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const size_t q = base + (size_t)u * rsize;
-          idx[u] = q < order.total ? order.at((uint32_t)q) : -1;
-          if (idx[u] >= 0) gate.wait(p, (uint32_t)idx[u], chunk, sub, tag, sg);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u)
+          const uint32_t q = t0 + (uint32_t)u * blockDim.x + threadIdx.x;
+          idx[u] = q < order.total ? order.at(q) : -1;
           if (idx[u] >= 0) v[u] = ld_poll_v4(xin + idx[u] * 16);
+        }
 #pragma unroll
         for (int u = 0; u < U; ++u)
           if (idx[u] >= 0) st_v4((char*)p.out + idx[u] * 16, v[u]);
