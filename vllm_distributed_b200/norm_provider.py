@@ -19,11 +19,16 @@ PROVIDER = "b200c"
 _PATCHED_ATTR = "_b200c_ir_priority_patched"
 
 
+_DTYPES = (torch.bfloat16, torch.float16, torch.float32)
+
+
 def _takes(x: Tensor, weight: Tensor | None) -> bool:
-    from .comm import DTYPE_CODE
+    # on the dispatch hot path (vllm/ir/op.py:321): cheapest tests first
+    if not x.is_cuda or x.dtype not in _DTYPES or not x.is_contiguous():
+        return False
     row_bytes = x.shape[-1] * x.element_size() if x.dim() else 0
-    return (x.is_cuda and x.dtype in DTYPE_CODE and x.numel() > 0 and x.is_contiguous()
-            and row_bytes % 16 == 0 and row_bytes // 16 <= 2048 and x.data_ptr() % 16 == 0
+    return (row_bytes % 16 == 0 and 0 < row_bytes <= 2048 * 16 and x.numel() > 0
+            and x.data_ptr() % 16 == 0
             and (weight is None or (weight.dtype == x.dtype and weight.is_contiguous()
                                     and weight.data_ptr() % 16 == 0)))
 
