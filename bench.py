@@ -272,12 +272,36 @@ def run_ours(args) -> dict:
         checks["step_norm_out"] = e_y <= 1e-2
         checks["logits_gather_bit_exact"] = bool(torch.equal(logits_full, logits_ref))
         worst = max(worst, e_r, e_y)
+        # Informational, never gating: the reference's own custom all-reduce kernels (K1/K2,
+        # fp32 accumulation in rank order, one rounding) on the same input must give the SAME BITS
+        # as this library's all-reduce -- the GPU-box oracle of SURVEY 8c.
+        code, why = 0, "unavailable"   # 0 unavailable, 1 differs, 2 same bits
+        try:
+            from vllm.distributed.device_communicators.custom_all_reduce import CustomAllreduce
+            ca = CustomAllreduce(group=cpu_group, device=dev, max_size=8 << 20)
+            if ca.disabled:
+                why = "unavailable: vLLM custom all-reduce disabled itself on this box"
+            else:
+                xs_half = x[0][: max(1, B // 2)].contiguous()  # under the reference's 1 MiB cap at TP=8
+                want = ca.custom_all_reduce(xs_half)
+                got = comm.all_reduce(xs_half)
+                torch.cuda.synchronize()
+                if want is None:
+                    why = "unavailable: the reference kernel does not take this size"
+                else:
+                    code = 2 if torch.equal(got, want) else 1
+                ca.close()
+        except Exception as e:  # noqa: BLE001 -- a comparator problem must not fail the bench
+            why = f"unavailable: {type(e).__name__}: {str(e)[:120]}"
+        st = torch.tensor([code], dtype=torch.int32, device=dev)
+        dist.all_reduce(st, op=dist.ReduceOp.MIN)   # the one collective of this block, on every path
+        bitwise = {2: True, 1: False}.get(int(st.item()), why)
         flag = torch.tensor([0 if all(checks.values()) else 1], dtype=torch.int32, device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MAX)
         w = torch.tensor([worst], dtype=torch.float64, device=dev)
         dist.all_reduce(w, op=dist.ReduceOp.MAX)
         parity = {"ok": int(flag.item()) == 0, "max_rel": round(float(w.item()), 6),
-                  "checks_rank0": checks,
+                  "checks_rank0": checks, "bitwise_vs_vllm_custom_all_reduce": bitwise,
                   "against": "NCCL all_reduce (fp32-upcast sum rounded once; and, first call, the bf16 sum) / "
                              "all_gather_into_tensor + fp32 torch norm, every rank"}
         if not parity["ok"]:

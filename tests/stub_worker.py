@@ -25,5 +25,10 @@ class StubWorker:
     def sample_tokens(self, grammar_output):
         return {"rank": self.rank, "sampled": grammar_output}
 
+    def nap(self, seconds):
+        import time
+        time.sleep(seconds)
+        return "rested"
+
     def shutdown(self):
         pass

@@ -84,6 +84,26 @@ print("dispatch ok")
 '''
 
 
+def test_variant_thresholds_from_a_measured_table():
+    """choose_thresholds: the AUTO crossovers as a pure function of a measured table."""
+    from vllm_distributed_b200.comm import choose_thresholds
+    K, M = 1 << 10, 1 << 20
+    # the TP=8 sweep of profiles/r2_sweep_tp8_final.json, abridged
+    table = {16 * K: {"oneshot": 6.25, "twoshot": 9.18}, 256 * K: {"oneshot": 8.77, "twoshot": 11.08},
+             1 * M: {"oneshot": 17.91, "twoshot": 12.44}, 4 * M: {"oneshot": 61.9, "twoshot": 21.8, "nvls": 33.6},
+             32 * M: {"twoshot": 119.3, "nvls": 134.8}, 64 * M: {"twoshot": 218.8, "nvls": 197.6}}
+    assert choose_thresholds(table) == {"oneshot_max_bytes": 256 * K, "nvls_min_bytes": 64 * M}
+    # one-shot never wins / NVLS never wins / a noisy one-shot win above the crossover is ignored
+    assert choose_thresholds({1 * M: {"oneshot": 9.0, "twoshot": 8.0}}) == {"oneshot_max_bytes": 0, "nvls_min_bytes": -1}
+    noisy = {64 * K: {"oneshot": 5.0, "twoshot": 7.0}, 1 * M: {"oneshot": 9.0, "twoshot": 8.0},
+             2 * M: {"oneshot": 8.9, "twoshot": 9.0}}
+    assert choose_thresholds(noisy)["oneshot_max_bytes"] == 64 * K
+    # NVLS must win at EVERY larger size to be chosen from a size on
+    gap = {8 * M: {"twoshot": 40.0, "nvls": 39.0}, 32 * M: {"twoshot": 100.0, "nvls": 110.0},
+           64 * M: {"twoshot": 200.0, "nvls": 180.0}}
+    assert choose_thresholds(gap)["nvls_min_bytes"] == 64 * M
+
+
 def test_dispatch_rules():
     out = subprocess.run([sys.executable, "-c", CODE % ROOT], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-3000:]

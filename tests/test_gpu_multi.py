@@ -84,6 +84,15 @@ def _worker(rank, world, port, q):
                 comm.send(msg, (rank + 1) % world)
             torch.cuda.synchronize()
             ok &= bool((got.float() == float((rank - 1) % world)).all())
+        # AUTO thresholds from a table measured on this box: every rank must choose the same
+        # ones, and AUTO must stay bit-exact afterwards
+        tab = comm.calibrate(cpu_group, hidden=4096, iters=4, sizes=(64 << 10, 1 << 20, 4 << 20))
+        chosen = [None] * world
+        dist.all_gather_object(chosen, tab["chosen"], group=cpu_group)
+        ok &= all(c == chosen[0] for c in chosen)
+        notes.append(f"calibrated: {tab['chosen']}")
+        xs = [torch.randn(300, 4096, generator=torch.Generator().manual_seed(1234 + r)).bfloat16() for r in range(world)]
+        ok &= torch.equal(comm.all_reduce(xs[rank].to(dev)).cpu(), oracle.all_reduce(xs))
         comm.check_health()
         if rank == 0:
             print(f"[world {world}] NVLS multicast {'attached' if comm.nvls else 'NOT available: ' + getattr(comm, 'nvls_reason', '')}")

@@ -104,6 +104,16 @@ assert ex.execute_model("sched-out") == {"rank": 1, "echo": "sched-out"}
 assert ex.sample_tokens("grammar") == {"rank": 1, "sampled": "grammar"}
 fut = ex.sample_tokens("g2", non_block=True)
 assert fut.result(timeout=30) == {"rank": 1, "sampled": "g2"}
+# `timeout` is honoured under the shim (the launcher itself ignores it, launch.py:351-384)
+import time
+t0 = time.monotonic()
+try:
+    ex.collective_rpc("nap", timeout=0.3, args=(2.0,))
+    raise SystemExit("expected a TimeoutError")
+except TimeoutError as e:
+    assert time.monotonic() - t0 < 1.5 and "nap" in str(e), e
+assert ex.collective_rpc("nap", timeout=30, args=(0.01,)) == ["rested", "rested"]   # workers are fine afterwards
+ex.check_health()                                                                  # timeout=10 now means something
 print("BRINGUP REMOTE OK", flush=True)
 os._exit(0)
 '''

@@ -125,6 +125,32 @@ def rms_norm(x: torch.Tensor, gamma: torch.Tensor, eps: float,
     return out
 
 
+def choose_thresholds(table: dict[int, dict[str, float]]) -> dict[str, int]:
+    """From measured us per call {bytes: {"oneshot": t, "twoshot": t[, "nvls": t]}} pick
+    `oneshot_max_bytes` = the largest size up to which one-shot never lost to two-shot (scanning
+    upwards, so one noisy point higher up cannot extend it), and `nvls_min_bytes` = the smallest
+    size from which the in-switch variant wins at every larger measured size (-1 if it never does).
+    Pure function of its input: every rank feeds it the same max-over-ranks table and gets the
+    same answer, which the protocol requires (all ranks must run the same variant)."""
+    sizes = sorted(table)
+    oneshot_max = 0
+    for sz in sizes:
+        t = table[sz]
+        if "oneshot" in t and t["oneshot"] <= t["twoshot"]:
+            oneshot_max = sz
+        else:
+            break
+    nvls_min = -1
+    for sz in reversed(sizes):
+        t = table[sz]
+        best_push = min(v for k, v in t.items() if k != "nvls")
+        if "nvls" in t and t["nvls"] < best_push:
+            nvls_min = sz
+        else:
+            break
+    return {"oneshot_max_bytes": oneshot_max, "nvls_min_bytes": nvls_min}
+
+
 class B200Comm:
     """One rank of a TP (or PP) group.  Owns its arena and the peers' IPC mappings."""
 
@@ -226,6 +252,55 @@ class B200Comm:
 
     def check_health(self) -> None:
         C.check(C.lib().b200c_query_error(self.ctx))
+
+    def calibrate(self, cpu_group, hidden: int = 8192, iters: int = 12,
+                  sizes: tuple[int, ...] = (64 << 10, 256 << 10, 512 << 10, 1 << 20, 2 << 20, 4 << 20)) -> dict:
+        """Measure the fused call per variant at a few sizes ON THIS BOX and set the AUTO
+        thresholds from the result (SURVEY 8d "variant selection": a measured table written at
+        init, not constants tuned on someone else's machine -- the compiled-in defaults come from
+        one 8 x B200 box).  Collective: every rank of the group calls it at the same point.
+        About 0.2 s.  NVLS sizes (32 / 64 MiB) are added when a multicast buffer is attached
+        and the arena is large enough."""
+        import torch.distributed as dist
+        dev = self.device
+        sizes = tuple(s for s in sizes if s <= self.max_bytes)
+        if self.nvls:
+            sizes += tuple(s for s in (32 << 20, 64 << 20) if s <= self.max_bytes)
+        gamma = torch.ones(hidden, dtype=torch.bfloat16, device=dev)
+        table: dict[int, dict[str, float]] = {}
+        for sz in sizes:
+            tokens = max(1, sz // (hidden * 2))
+            x = torch.zeros(tokens, hidden, dtype=torch.bfloat16, device=dev)
+            res = torch.zeros_like(x)
+            out = torch.empty_like(x)
+            names = [("twoshot", C.TWOSHOT)]
+            if x.numel() * 2 * self.world <= 2 * self.max_bytes and sz <= (4 << 20):
+                names.append(("oneshot", C.ONESHOT))
+            if self.nvls and sz >= (4 << 20):
+                names.append(("nvls", C.NVLS))
+            row = {}
+            for name, code in names:
+                for _ in range(3):
+                    self.all_reduce_add_rmsnorm_into(x, res, gamma, 1e-5, out, code)
+                torch.cuda.synchronize(dev)
+                dist.barrier(group=cpu_group)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(iters):
+                    self.all_reduce_add_rmsnorm_into(x, res, gamma, 1e-5, out, code)
+                b.record()
+                torch.cuda.synchronize(dev)
+                t = torch.tensor([a.elapsed_time(b) * 1e3 / iters], dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)   # same number on every rank
+                row[name] = float(t.item())
+            table[x.numel() * 2] = row
+        chosen = choose_thresholds(table)
+        if chosen["oneshot_max_bytes"] > 0:
+            self.set_tuning(C.TUNE_ONESHOT_MAX_BYTES, chosen["oneshot_max_bytes"])
+        if self.nvls:
+            self.set_tuning(C.TUNE_NVLS_MIN_BYTES, chosen["nvls_min_bytes"])
+        self.variant_table = {"us_per_call": table, "chosen": chosen}
+        return self.variant_table
 
     # ---- predicates the communicator uses to decide between this path and NCCL ----
     def can_all_reduce(self, x: torch.Tensor) -> bool:

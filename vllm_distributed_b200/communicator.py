@@ -80,6 +80,9 @@ class B200Communicator(CudaCommunicator):
         # -- instead of serving tokens computed from garbage.
         self.b200.set_tuning(C.TUNE_SPIN_TIMEOUT_MS, int(os.environ.get("B200C_SPIN_TIMEOUT_MS", 300000)))
         self.b200.set_tuning(C.TUNE_TRAP_ON_TIMEOUT, int(os.environ.get("B200C_TRAP_ON_TIMEOUT", 1)))
+        if kind == "tp" and os.environ.get("B200C_CALIBRATE", "0") == "1":
+            chosen = self.b200.calibrate(cpu_group)["chosen"]
+            logger.info("b200c: AUTO thresholds measured on this box: %s", chosen)
         logger.info("b200c: %s group of %d ranks on NVLink arenas (%s)%s", kind, self.world_size,
                     ", ".join(f"{k}={v >> 20} MiB" for k, v in sizes.items()),
                     ", NVLS multicast attached" if self.b200.nvls else "")

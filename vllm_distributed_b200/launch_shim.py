@@ -117,9 +117,32 @@ def adapt_executor(executor_cls) -> None:
       * supports_pp: the engine refuses pipeline parallelism otherwise (arg_utils.py:2265-2268);
       * sample_tokens: 0.22 samples in a second RPC; like execute_model (launch.py:322-336) the
         answer must come from the first TP worker of the LAST pipeline stage (output_rank), not
-        from worker 0 as the base class would take it.
+        from worker 0 as the base class would take it;
+      * timeout: the launcher's collective_rpc accepts `timeout` and ignores it (launch.py:351-384:
+        `f.result()` without a bound -- its own check_health passes timeout=10 to no effect).
+        The wrapper below takes the launcher's futures (its `non_block=True` path) and waits for
+        them with the deadline, raising TimeoutError like vLLM's own executors do.
     """
     executor_cls.supports_pp = True
+
+    orig_rpc = executor_cls.__dict__.get("collective_rpc")
+    if orig_rpc is not None and not getattr(orig_rpc, "_b200c_timeout", False):
+        import concurrent.futures
+        import time
+
+        def collective_rpc(self, method, timeout=None, args=(), kwargs=None, non_block=False,
+                           unique_reply_rank=None):
+            if timeout is None or non_block:
+                return orig_rpc(self, method, timeout, args, kwargs, non_block, unique_reply_rank)
+            futures = orig_rpc(self, method, timeout, args, kwargs, True, unique_reply_rank)
+            deadline = time.monotonic() + timeout
+            try:
+                return [f.result(timeout=max(0.0, deadline - time.monotonic())) for f in futures]
+            except concurrent.futures.TimeoutError as e:
+                name = method if isinstance(method, str) else getattr(method, "__name__", "callable")
+                raise TimeoutError(f"RPC call to {name} timed out after {timeout} s") from e
+        collective_rpc._b200c_timeout = True
+        executor_cls.collective_rpc = collective_rpc
 
     def sample_tokens(self, grammar_output, non_block: bool = False):
         (output,) = self.collective_rpc("sample_tokens", args=(grammar_output,),
