@@ -73,7 +73,73 @@ print("fusion pass ok")
 '''
 
 
+_RESULT = {}
+
+
+def _run_once():
+    """Both scripts in ONE interpreter (importing vLLM costs ~20 s): the hand-built graphs, then
+    the run inside Inductor."""
+    if not _RESULT:
+        import shutil
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else shutil.which("g++")
+        code = CODE % ROOT + ("\n" + INDUCTOR_CODE % ROOT if cxx else "")
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900,
+                             env=dict(os.environ, **({"CXX": cxx} if cxx else {})))
+        _RESULT.update(rc=out.returncode, out=out.stdout, err=out.stderr, cxx=cxx)
+    return _RESULT
+
+
 def test_fusion_pass_rewrites_the_pair_and_nothing_else():
-    out = subprocess.run([sys.executable, "-c", CODE % ROOT], capture_output=True, text=True, timeout=600)
-    assert out.returncode == 0, out.stderr[-3000:]
-    assert "fusion pass ok" in out.stdout
+    r = _run_once()
+    assert "fusion pass ok" in r["out"], r["err"][-3000:]
+
+
+INDUCTOR_CODE = r'''
+import sys, weakref; sys.path.insert(0, %r)
+import torch
+import vllm.ir.ops
+from vllm import ir
+import vllm.distributed.parallel_state as ps
+from vllm_distributed_b200 import plugin, fusion_pass, comm as bc
+plugin._register_fused_op()
+
+# a one-rank stand-in for the TP group: all_reduce is the identity and there is no device
+# communicator, so the fused op takes its local-norm branch -- served here by vLLM's native
+# definition instead of the CUDA kernel (this box has no GPU)
+class Group:
+    world_size = 1; device_communicator = None; unique_name = "tp:0"
+    def _all_reduce_out_place(self, t): return t.clone()
+group = Group()
+ps._groups["tp:0"] = weakref.ref(group)
+def cpu_norm(x, r, w, eps):
+    y, r2 = ir.ops.fused_add_rms_norm.impls["native"].impl_fn(x, r, w, eps)
+    x.copy_(y); r.copy_(r2); return x, r
+bc.fused_add_rms_norm_ = cpu_norm
+
+def layer_boundary(x, res, w):
+    ar = torch.ops.vllm.all_reduce(x * 2.0, "tp:0")            # stands for o_proj / down_proj + all-reduce
+    y, r2 = ir.ops.fused_add_rms_norm(ar, res, w, 1e-5)
+    return y + 1.0, r2
+
+x, res, w = torch.randn(4, 64).bfloat16(), torch.randn(4, 64).bfloat16(), torch.randn(64).bfloat16()
+ir.ops.fused_add_rms_norm.set_default(["native"])
+want = layer_boundary(x.clone(), res.clone(), w)
+rewrites = []
+import torch._inductor.config as ic
+with ic.patch(post_grad_custom_post_pass=lambda g: rewrites.append(fusion_pass.fuse_allreduce_rmsnorm(g))):
+    got = torch.compile(layer_boundary, backend="inductor", fullgraph=True)(x.clone(), res.clone(), w)
+assert sum(rewrites) == 1, rewrites
+assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+print("inductor ok")
+'''
+
+
+def test_fusion_pass_inside_real_inductor():
+    """The pass as Inductor's post_grad_custom_post_pass on a traced layer boundary, compiled with
+    the CPU backend and executed: one rewrite, the auto_functionalized call of the fused op survives
+    Inductor's own decomposition, results bit-identical to eager."""
+    import pytest
+    r = _run_once()
+    if not r["cxx"]:
+        pytest.skip("no C++ compiler for Inductor's CPU backend")
+    assert r["rc"] == 0 and "inductor ok" in r["out"], r["err"][-3000:]

@@ -146,6 +146,61 @@ def test_pp_channel_matches_vllm_golden(golden_dir, name, tp, pp):
     assert receivers == tp
 
 
+def _ring_worker(rank, world, port, q):
+    """pp_channel's shared-memory object ring on its own (no vLLM): first message over the
+    group's send_object, then the ring -- wrap-around with a slow reader, a payload too large for
+    a slot (falls back to send_object for that message), and the same-as-before marker."""
+    sys.path.insert(0, ROOT)
+    import pickle
+    import time
+    import torch.distributed as dist
+    from vllm_distributed_b200 import pp_channel
+    dist.init_process_group("gloo", rank=rank, world_size=world, init_method=f"tcp://127.0.0.1:{port}")
+
+    class Group:
+        rank_in_group = rank
+
+        def send_object(self, obj, dst):
+            t = torch.frombuffer(bytearray(pickle.dumps(obj)), dtype=torch.uint8)
+            dist.send(torch.tensor([t.numel()]), dst=dst)
+            dist.send(t, dst=dst)
+
+        def recv_object(self, src):
+            n = torch.empty(1, dtype=torch.long)
+            dist.recv(n, src=src)
+            t = torch.empty(int(n.item()), dtype=torch.uint8)
+            dist.recv(t, src=src)
+            return pickle.loads(t.numpy().tobytes())
+
+    g = Group()
+    big = "x" * (pp_channel.ShmObjectChannel.SLOT_BYTES + 100)
+    msgs = [("first", 0)] + [("m", i) for i in range(40)] + [("big", big), ("after", 1), ("after", 1), ("after", 1)]
+    paths, got = [], []
+    if rank == 0:
+        for m in msgs:
+            paths.append(pp_channel.send_meta(g, m, 1))
+        shm_file = g._b200c_meta_channels[("send", 1)].path
+    else:
+        for i, _ in enumerate(msgs):
+            if i == 5:
+                time.sleep(0.5)          # the writer runs 16 slots ahead and has to wait for acks
+            got.append(pp_channel.recv_meta(g, 0))
+        shm_file = None
+    dist.barrier()
+    q.put((rank, (paths, got == msgs, shm_file is None or not os.path.exists(shm_file))))
+    dist.destroy_process_group()
+
+
+def test_pp_metadata_ring_wraps_falls_back_and_repeats():
+    res = _spawn(_ring_worker, 2)
+    paths, _, unlinked = res[0]
+    assert paths[0] == "gloo" and set(paths[1:41]) == {"shm"} and len(paths) == 45
+    assert paths[41] == "gloo"                      # too large for a slot: that one message over gloo
+    assert paths[42:] == ["shm", "shm-same", "shm-same"]
+    assert unlinked                                  # the /dev/shm file is gone once both sides mapped it
+    assert res[1][1]                                 # the receiver saw every message, in order
+
+
 # ---- bench.py reference arm ------------------------------------------------------------------------
 
 def test_bench_reference_arm_prints_contract_line():

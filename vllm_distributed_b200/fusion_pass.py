@@ -13,8 +13,9 @@ active the graph already holds the fused op and this pass finds nothing to do.
 
 Hooks: (i) `CompilationConfig(inductor_passes={"post_grad_custom_post_pass":
 "vllm_distributed_b200.b200c_fusion_pass"})` -- the documented seam (config/compilation.py:582-587,
-925-940); (ii) plugin.register() appends the pass to PostGradPassManager itself unless
-B200C_FUSION_PASS=0, so that a user of the plugin does not have to edit the config.  Set
+925-940); (ii) with B200C_FUSION_PASS=1 plugin.register() appends the pass to PostGradPassManager
+itself, so that a user of the plugin does not have to edit the config (opt-in: the rewrite is
+pinned on hand-built graphs but has not been run end to end on a non-Llama model yet).  Set
 `pass_config.fuse_allreduce_rms=False` so that FlashInfer's pass does not claim the same pairs first.
 """
 from __future__ import annotations

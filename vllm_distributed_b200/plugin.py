@@ -122,7 +122,9 @@ def register() -> None:
     if os.environ.get("B200C_PP_CHANNEL", "1") == "1":
         from . import pp_channel
         pp_channel.apply()
-    if os.environ.get("B200C_FUSION_PASS", "1") == "1":
+    if os.environ.get("B200C_FUSION_PASS", "0") == "1":
+        # opt-in: pinned on hand-built graphs (tests/test_fusion_pass_cpu.py) but not yet run end
+        # to end on a non-Llama model, so it does not rewrite anybody's graphs by default
         from . import fusion_pass
         fusion_pass.install_in_pass_manager()
     _hook_worker_health()
