@@ -827,12 +827,13 @@ __device__ __forceinline__ void ar_body(const RankParams& p) {
 // rounds ties differently from round-to-nearest-even and its summation order is unspecified, so
 // this variant is tolerance-parity with the oracle (north_star's 1e-2), never bit-parity; all
 // ranks still get identical bits because each sum is computed once and broadcast.
-// Consumers wait per CTA, not per thread: ONE thread polls the slice's flag (with a short sleep
-// between polls) and the CTA barrier hands the result to the others.  Every thread polling the
-// same few flag lines with system-scope acquires (130 k threads on 64 lines) slowed the whole
-// kernel down by a third (tools/nvls_probe.py: 169 us without consumers, 242 us with).
+// Consumers wait per CTA, not per thread: ONE thread polls the flags of the slices a vector
+// range lies in (with a short sleep between polls) and the CTA barrier hands the result to the
+// others, which keeps 130 k threads off 64 flag lines.  A range usually lies in one slice (a row
+// is far smaller than a slice wherever this variant is worth using); for tiny messages it can
+// cross many (one row over every owner's chunk), and then EVERY slice it touches is waited for.
 struct SliceGate {
-  uint32_t seen_a = 0xffffffffu, seen_b = 0xffffffffu;  // slice ids this CTA has found complete
+  uint32_t seen = 0xffffffffu;  // the one slice this CTA last found complete
   template <typename P>
   static __device__ __forceinline__ void poll(const P& p, uint32_t id, uint32_t tag, SpinGuard& sg) {
     const uint32_t* f = reinterpret_cast<const uint32_t*>(
@@ -851,14 +852,20 @@ struct SliceGate {
   __device__ __forceinline__ void wait(const P& p, uint32_t first, uint32_t last, uint32_t chunk,
                                        uint32_t sub, uint32_t tag, SpinGuard& sg) {
     const uint32_t a = slice_of(first, chunk, sub), b = slice_of(last, chunk, sub);
-    if ((a == seen_a || a == seen_b) && (b == seen_a || b == seen_b)) return;
+    if (a == seen && b == seen) return;
     if (threadIdx.x == 0) {
-      poll(p, a, tag, sg);
-      if (b != a) poll(p, b, tag, sg);
+      // walk the range slice by slice: idx always is the first vector of the range inside a slice
+      uint32_t idx = first;
+      for (;;) {
+        poll(p, slice_of(idx, chunk, sub), tag, sg);
+        const uint32_t o = idx / chunk, g = (idx - o * chunk) / sub;
+        const uint32_t next = o * chunk + min((g + 1u) * sub, chunk);  // first vector of the next slice
+        if (next > last) break;
+        idx = next;
+      }
     }
     __syncthreads();
-    seen_a = a;
-    seen_b = b;
+    seen = (a == b) ? a : 0xffffffffu;
   }
 };
 
