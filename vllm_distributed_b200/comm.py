@@ -15,9 +15,11 @@ from . import _cabi as C
 
 DTYPE_CODE = {torch.bfloat16: C.BF16, torch.float16: C.F16, torch.float32: C.F32}
 
-# Arena defaults, sized for B200's 180 GB: 64 MiB messages cover [4096 tok x 8192] bf16
-# (three rotating regions of 2x that), 72 MiB covers the 70B lm_head gather at batch 256.
-DEFAULT_MAX_BYTES = int(os.environ.get("B200C_MAX_BYTES", 64 << 20))
+# Arena defaults, sized for B200's 180 GB: 128 MiB messages cover [8192 tok x 8192] bf16, i.e.
+# vLLM's default max_num_batched_tokens of prefill at the 70B hidden size (with 64 MiB that
+# point silently went to the stock path; three rotating regions of 2x that), 72 MiB covers the
+# 70B lm_head gather at batch 256.
+DEFAULT_MAX_BYTES = int(os.environ.get("B200C_MAX_BYTES", 128 << 20))
 DEFAULT_AG_BYTES = int(os.environ.get("B200C_AG_BYTES", 72 << 20))
 DEFAULT_P2P_BYTES = int(os.environ.get("B200C_P2P_BYTES", 16 << 20))
 
