@@ -146,6 +146,60 @@ def test_pp_channel_matches_vllm_golden(golden_dir, name, tp, pp):
     assert receivers == tp
 
 
+def _nvls_attach_worker(rank, world, port, q):
+    """B200Comm.try_attach_nvls with torch's symmetric memory and the C library mocked: the
+    group attaches the in-switch buffer only if EVERY rank got a multicast pointer."""
+    sys.path.insert(0, ROOT)
+    import types
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+    from vllm_distributed_b200 import _cabi as C
+    from vllm_distributed_b200 import comm as bc
+    dist.init_process_group("gloo", rank=rank, world_size=world, init_method=f"tcp://127.0.0.1:{port}")
+    calls = []
+
+    class FakeLib:
+        def b200c_nvls_bytes(self, max_bytes, out):
+            out._obj.value = 32 * 1024 + max_bytes + 256
+            return 0
+
+        def b200c_attach_nvls(self, ctx, uc, mc, nbytes):
+            calls.append((uc, mc, nbytes))
+            return 0
+
+        def b200c_set_tuning(self, ctx, key, value):
+            calls.append(("tune", key, value))
+            return 0
+    C._lib = FakeLib()
+
+    class _NoDev:
+        def __enter__(self): return self
+        def __exit__(self, *a): return False
+    torch.cuda.device = lambda d: _NoDev()
+    outcomes = []
+    for mc_of_rank in ({0: 0x7000, 1: 0}, {0: 0x7000, 1: 0x7100}):
+        symm_mem.enable_symm_mem_for_group = lambda name: None
+        symm_mem.empty = lambda n, dtype=None, device=None: types.SimpleNamespace(data_ptr=lambda: 0x1000 + rank, numel=n)
+        symm_mem.rendezvous = lambda buf, name, mc=mc_of_rank: types.SimpleNamespace(multicast_ptr=mc[rank])
+        c = object.__new__(bc.B200Comm)
+        c.rank, c.world, c.device, c.max_bytes, c.ctx = rank, world, torch.device("cpu"), 1 << 20, None
+        c.nvls, c._nvls_buf = False, None
+        calls.clear()
+        ok = c.try_attach_nvls(dist.group.WORLD, types.SimpleNamespace(group_name="g0"))
+        outcomes.append((ok, c.nvls, list(calls)))
+    bc.B200Comm.__del__ = lambda self: None
+    q.put((rank, outcomes))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_nvls_attach_is_all_or_nothing():
+    res = _spawn(_nvls_attach_worker, 2)
+    for rank, ((ok1, nvls1, calls1), (ok2, nvls2, calls2)) in res.items():
+        assert (ok1, nvls1, calls1) == (False, False, [])            # rank 1 had no multicast pointer: nobody attaches
+        assert ok2 and nvls2 and calls2 == [(0x1000 + rank, 0x7000 + 0x100 * rank, 32 * 1024 + (1 << 20) + 256)]
+
+
 def _ring_worker(rank, world, port, q):
     """pp_channel's shared-memory object ring on its own (no vLLM): first message over the
     group's send_object, then the ring -- wrap-around with a slow reader, a payload too large for
