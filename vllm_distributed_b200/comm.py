@@ -216,18 +216,33 @@ class B200Comm:
         mc = uc = 0
         buf = None
         why = ""
+        # step 1, local: allocate.  The ranks agree on the outcome BEFORE the rendezvous, which is
+        # a collective: a rank that failed here must not leave its peers waiting in it.
         try:
+            import warnings
             import torch.distributed._symmetric_memory as symm_mem
             name = device_group.group_name
-            try:
-                symm_mem.enable_symm_mem_for_group(name)
-            except Exception:  # noqa: BLE001 -- no-op or deprecated in newer torch
-                pass
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                try:
+                    symm_mem.enable_symm_mem_for_group(name)
+                except Exception:  # noqa: BLE001 -- no-op or deprecated in newer torch
+                    pass
             with torch.cuda.device(self.device):
                 buf = symm_mem.empty(need.value, dtype=torch.uint8, device=self.device)
+        except Exception as e:  # noqa: BLE001 -- the NVLS variant is optional
+            why = f"{type(e).__name__}: {e}"
+        allocated: list = [None] * self.world
+        dist.all_gather_object(allocated, buf is not None, group=cpu_group)
+        if not all(allocated):
+            self.nvls_reason = why or "symmetric-memory allocation failed on some rank"
+            return False
+        # step 2, collective: rendezvous; a fabric without multicast answers with a null pointer
+        try:
+            with torch.cuda.device(self.device):
                 hdl = symm_mem.rendezvous(buf, name)
             mc, uc = int(hdl.multicast_ptr), int(buf.data_ptr())
-        except Exception as e:  # noqa: BLE001 -- the NVLS variant is optional
+        except Exception as e:  # noqa: BLE001
             why = f"{type(e).__name__}: {e}"
         oks: list = [None] * self.world
         dist.all_gather_object(oks, bool(mc), group=cpu_group)
