@@ -105,6 +105,6 @@ def test_variant_thresholds_from_a_measured_table():
 
 
 def test_dispatch_rules():
-    out = subprocess.run([sys.executable, "-c", CODE % ROOT], capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0, out.stderr[-3000:]
-    assert "dispatch ok" in out.stdout
+    from _shared_vllm_run import run_all
+    r = run_all()
+    assert "dispatch ok" in r["out"], r["err"][-3000:]

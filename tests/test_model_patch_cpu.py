@@ -106,6 +106,6 @@ print("model patch ok")
 
 
 def test_layer_fusion_plan():
-    out = subprocess.run([sys.executable, "-c", CODE % ROOT], capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0, out.stderr[-3000:]
-    assert "model patch ok" in out.stdout
+    from _shared_vllm_run import run_all
+    r = run_all()
+    assert "model patch ok" in r["out"], r["err"][-3000:]

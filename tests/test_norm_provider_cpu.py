@@ -52,6 +52,6 @@ print("norm provider ok")
 
 
 def test_norm_provider_registration_dispatch_and_priority():
-    out = subprocess.run([sys.executable, "-c", CODE % ROOT], capture_output=True, text=True, timeout=600)
-    assert out.returncode == 0, out.stderr[-3000:]
-    assert "norm provider ok" in out.stdout
+    from _shared_vllm_run import run_all
+    r = run_all()
+    assert "norm provider ok" in r["out"], r["err"][-3000:]
