@@ -24,15 +24,16 @@ DEFAULT_AG_BYTES = int(os.environ.get("B200C_AG_BYTES", 72 << 20))
 DEFAULT_P2P_BYTES = int(os.environ.get("B200C_P2P_BYTES", 16 << 20))
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
-
-
 try:  # raw handle of the current stream of a device: about 10x cheaper than the Stream object
     _raw_stream = torch._C._cuda_getCurrentRawStream
 except AttributeError:  # pragma: no cover -- older / CPU-only torch builds
     def _raw_stream(index: int) -> int:
         return torch.cuda.current_stream(index).cuda_stream
+
+
+def _stream() -> int:
+    """The current stream of the current device (what every entry point launches on)."""
+    return _raw_stream(torch.cuda.current_device())
 
 _NORM_FNS: list = []
 
